@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""Benchmark of the finite_difference time-stepping hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload c3|c2|c4]
+
+One "step" is one time step of the model (every grid point advanced once).
+Default workload (N=1): BASELINE.json configs[2], 3-D heat diffusion 512^3
+fp64, 7-point stencil, periodic -- the configuration the north-star target is
+quoted on.  Prints ONE JSON line (see DESIGN.md "Measurement").
+
+  value      point-updates/s, state resident in HBM, CUDA events on the
+             launching stream around exactly K steps driven through the public
+             `finite_difference` API (the recorded-statement layer included)
+  e2e        the same K steps through the public API with HOST buffers:
+             initial condition uploaded from pinned host memory, final level
+             read back to the host, both inside the timed region
+  roofline   algorithmic bytes (16 B/point: one read + one write of the state)
+             over the measured step time, against the measured HBM copy peak
+  cpu_baseline  the numpy port of the reference path (oracle/fd_numpy.py) on
+             a bounded sample, on this box's host cores (numpy: 1 core)
+"""
+
+from __future__ import annotations
+
+import argparse
+import contextlib
+import io
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "finite-difference_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    # name: (description, spatial shape, bytes per point update)
+    "c3": ("3-D heat diffusion 512^3 fp64, 7-point stencil, periodic (BASELINE.json configs[2])", (512, 512, 512), 16),
+    "c2": ("2-D heat diffusion 8192^2 fp64, 5-point stencil, fixed BCs (BASELINE.json configs[1])", (8192, 8192), 16),
+    "c4": ("2-D wave equation 8192^2 fp64, n_time_ders=2, 9-point-per-axis stencils, periodic (BASELINE.json configs[3])",
+           (8192, 8192), 32),
+}
+K_DIFF, DT = 0.1, 1e-3
+
+
+# ------------------------------------------------------------------ helpers
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(workload):
+    """dram bytes per launch of the dominant kernel from the committed ncu
+    --set full capture (profiles/traffic.json), or None."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.isfile(path):
+        try:
+            return json.load(open(path)).get(workload, {}).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region."""
+    QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------- the B200 model
+def build_model(fd, workload, n_t, ic, history="last"):
+    """The workload written against the public API (what a user script does)."""
+    shape = WORKLOADS[workload][1]
+    names = ["x", "y", "z"][:len(shape)]
+    axes = {"t": np.arange(n_t) * DT}
+    for n, a in zip(shape, names):
+        axes[a] = np.arange(n) * 1.0
+    periodic = workload in ("c3", "c4")
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model(axes, "t", periodic=tuple(names) if periodic else (), history=history)
+        if workload == "c4":
+            u = fd.Field(m, "u", n_time_ders=2)
+            st = fd.Stencil(list(range(-4, 5)), 2)
+            u.set_IC_values(ic)
+            u.dot.set_IC("0")
+
+            def step():
+                acc = st.der(u.prev, names[0])
+                for a in names[1:]:
+                    acc = acc + st.der(u.prev, a)
+                u.dot.dot.assign_update(0.01 * acc)
+                u.dot.time_integrate_update()
+                u.time_integrate_update()
+                m.increment_time()
+            return m, u, step
+        T = fd.Field(m, "T", n_time_ders=1)
+        st = fd.Stencil([-1, 0, 1], 2)
+        T.set_IC_values(ic)
+        if not periodic:
+            for a in names:
+                T.set_BC("0", a, "start")
+                T.set_BC("0", a, "end")
+
+    def step():
+        acc = st.der(T.prev, names[0])
+        for a in names[1:]:
+            acc = acc + st.der(T.prev, a)
+        T.dot.assign_update(K_DIFF * acc)
+        T.time_integrate_update()
+        m.increment_time()
+    return m, T, step
+
+
+def cpu_port_rate(workload, shape, steps_timed=1):
+    """Numpy port of the reference path on this host: point-updates/s."""
+    from oracle import fd_numpy as O
+    ic = np.random.default_rng(0).random(shape)
+    # a 1-step run first as warm-up (page faults, numpy set-up), then the timed run
+    if workload == "c4":
+        O.run_wave(shape, 2, 0.01, 1e-2, ic, np.zeros(shape))
+        t0 = time.perf_counter()
+        O.run_wave(shape, 1 + steps_timed, 0.01, 1e-2, ic, np.zeros(shape))
+    else:
+        periodic = workload == "c3"
+        O.run_heat(shape, 2, periodic, K_DIFF, DT, ic)
+        t0 = time.perf_counter()
+        O.run_heat(shape, 1 + steps_timed, periodic, K_DIFF, DT, ic)
+    dt = time.perf_counter() - t0
+    return float(np.prod(shape)) * steps_timed / dt, dt
+
+
+def sample_shape(workload, target_points):
+    full = WORKLOADS[workload][1]
+    if np.prod(full) <= target_points:
+        return full
+    side = int(round(target_points ** (1.0 / len(full))))
+    side = max(32, side - side % 32)
+    return tuple(min(side, n) for n in full)
+
+
+# ------------------------------------------------------------------- arms
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    desc, shape, bpp = WORKLOADS[args.workload]
+    # bounded sample: K+W steps of the numpy port must end within a few minutes
+    rate_guess = 1.0e7
+    budget_s = 150.0
+    pts = rate_guess * budget_s / max(1, args.steps + args.warmup)
+    sshape = sample_shape(args.workload, pts)
+    from oracle import fd_numpy as O
+    ic = np.random.default_rng(0).random(sshape)
+    periodic = args.workload in ("c3", "c4")
+
+    def run(n_steps):
+        if args.workload == "c4":
+            O.run_wave(sshape, n_steps + 1, 0.01, 1e-2, ic, np.zeros(sshape))
+        else:
+            O.run_heat(sshape, n_steps + 1, periodic, K_DIFF, DT, ic)
+    run(args.warmup)
+    t0 = time.perf_counter()
+    run(args.steps)
+    elapsed = time.perf_counter() - t0
+    value = float(np.prod(sshape)) * args.steps / elapsed
+    sample = f"{'x'.join(map(str, sshape))} grid (same stencil, dtype and boundary kind), {args.steps} steps, full numpy history"
+    line = {
+        "impl": "reference", "metric": "grid-point updates/sec", "value": value, "unit": "point-updates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * elapsed / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "sample": sample, "host_threads": 1},
+        "cpu_baseline": {"value": value, "unit": "point-updates/s", "cores": 1, "kind": "port", "sample": sample,
+                         "host_cpus": os.cpu_count()},
+        "e2e": {"value": value, "unit": "point-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import finite_difference as fd
+    from finite_difference import _device
+
+    desc, shape, bpp = WORKLOADS[args.workload]
+    points = float(np.prod(shape))
+    K, W = args.steps, args.warmup
+
+    # ---- device-resident run --------------------------------------------
+    pinned = torch.empty(int(points), dtype=torch.float64, pin_memory=True)
+    ic = pinned.numpy().reshape(shape)
+    ic[...] = np.random.default_rng(rank).random(shape)
+    m, F, step = build_model(fd, args.workload, W + K + 2, ic)
+    for _ in range(W):
+        step()
+    m.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    launches0 = _device.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        ev0.record()
+        for _ in range(K):
+            step()
+        ev1.record()
+        torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    launches = _device.launch_count() - launches0
+    m.synchronize()
+    stats = dict(m._engine.stats)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    del m, F, step
+    torch.cuda.empty_cache()
+
+    # ---- end to end through the public API with host buffers -------------
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    m2, F2, step2 = build_model(fd, args.workload, K + 1, ic)
+    for _ in range(K):
+        step2()
+    final = F2.data_level(K)
+    m2.synchronize()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    assert final.shape == tuple(shape) and np.isfinite(final[::7]).all()
+    bytes_level = points * 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = world * points * K / (ms * 1e-3)
+    peak, peak_src = measured_peak()
+    achieved = points * bpp / (ms / K * 1e-3) / 1e9
+    line = {
+        "metric": "grid-point updates/sec", "value": value, "unit": "point-updates/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "grid_per_gpu": "x".join(map(str, shape)),
+                   "l2": "inputs larger than L2 (state level = %.0f MiB vs 126 MB L2)" % (points * 8 / 2 ** 20),
+                   "multi_gpu": "replicas (no halo exchange yet)" if world > 1 else "single GPU",
+                   "history": "last", "engine_stats": stats},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
+                     "frac_of_8TBs": achieved / 8000.0, "bytes_per_point_update": bpp},
+        "e2e": {"value": world * points * K / e2e_s, "unit": "point-updates/s",
+                "h2d_bytes_per_step": bytes_level / K, "d2h_bytes_per_step": bytes_level / K,
+                "seconds": e2e_s,
+                "includes": "model construction, IC upload from pinned host memory, K steps, final level read back"},
+        "gpu_launches": launches,
+        "clocks": clocks.summary(),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        sshape = sample_shape(args.workload, 1.4e8 if args.workload == "c3" else 6.8e7)
+        rate, secs = cpu_port_rate(args.workload, sshape)
+        line["cpu_baseline"] = {"value": rate, "unit": "point-updates/s", "cores": 1, "kind": "port",
+                                "sample": f"{'x'.join(map(str, sshape))} grid, 1 warm-up + 1 timed step "
+                                          f"({secs:.1f} s), full numpy history like the reference",
+                                "host_cpus": os.cpu_count()}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,116 @@
+"""Device plumbing: memory, streams, events and flag words, via PyTorch.
+
+PyTorch is used here only as a CUDA allocator / stream / event provider (and,
+for multi-GPU runs, for its NCCL process group).  All arithmetic happens in
+``libfd_b200.so``.  Nothing in this module computes on the CPU; if no CUDA
+device is available every entry point raises.
+"""
+
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from . import _native as nat
+
+_torch = None
+
+
+def torch():
+    global _torch
+    if _torch is None:
+        import torch as _t
+        _torch = _t
+    return _torch
+
+
+class NoDeviceError(RuntimeError):
+    pass
+
+
+def _torch_dtype(dtype):
+    t = torch()
+    return t.float32 if np.dtype(dtype) == np.float32 else t.float64
+
+
+class Device:
+    """One CUDA device: a compute stream, a copy (side) stream and the sticky
+    condition flags shared by every launch of a model."""
+
+    _instances = {}
+
+    @classmethod
+    def get(cls, index=None):
+        t = torch()
+        if not t.cuda.is_available():
+            raise NoDeviceError(
+                "finite_difference (B200 build) needs a CUDA device to advance a model; "
+                "there is no CPU fallback")
+        if index is None:
+            index = int(os.environ.get("LOCAL_RANK", "0")) % t.cuda.device_count() \
+                if "LOCAL_RANK" in os.environ else t.cuda.current_device()
+        if index not in cls._instances:
+            cls._instances[index] = cls(index)
+        return cls._instances[index]
+
+    def __init__(self, index):
+        t = torch()
+        self.index = index
+        self.dev = t.device("cuda", index)
+        t.cuda.set_device(self.dev)
+        # kernels run on torch's current stream so that torch.cuda.Event timing
+        # and NCCL ordering see them; copies to the host run on a side stream
+        self.copy_stream = t.cuda.Stream(device=self.dev)
+
+    # -- streams ---------------------------------------------------------
+    @property
+    def stream(self):
+        return torch().cuda.current_stream(self.dev)
+
+    @property
+    def stream_ptr(self):
+        return self.stream.cuda_stream
+
+    def synchronize(self):
+        torch().cuda.synchronize(self.dev)
+
+    # -- memory ----------------------------------------------------------
+    def empty(self, n, dtype):
+        return torch().empty(int(n), dtype=_torch_dtype(dtype), device=self.dev)
+
+    def zeros_i64(self, n):
+        t = torch()
+        return t.zeros(int(n), dtype=t.int64, device=self.dev)
+
+    def upload(self, array, dtype, out=None):
+        """Host ndarray -> device tensor (flattened, cast to ``dtype``)."""
+        t = torch()
+        host = np.ascontiguousarray(array, dtype=dtype).reshape(-1)
+        src = t.from_numpy(host)
+        if out is None:
+            out = self.empty(host.size, dtype)
+        out.copy_(src, non_blocking=False)
+        return out
+
+    def download(self, tensor, shape=None):
+        arr = tensor.detach().cpu().numpy()
+        return arr.reshape(shape) if shape is not None else arr
+
+    def pinned(self, shape, dtype):
+        """Pinned host ndarray (falls back to pageable if pinning fails)."""
+        t = torch()
+        n = int(np.prod(shape)) if len(shape) else 1
+        try:
+            buf = t.empty(n, dtype=_torch_dtype(dtype), pin_memory=True)
+        except RuntimeError:
+            buf = t.empty(n, dtype=_torch_dtype(dtype))
+        return buf, buf.numpy().reshape(shape)
+
+
+def ptr(tensor):
+    return 0 if tensor is None else tensor.data_ptr()
+
+
+def launch_count():
+    return int(nat.lib.fd_launch_count())

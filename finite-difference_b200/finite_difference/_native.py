@@ -1,0 +1,134 @@
+"""ctypes binding of ``libfd_b200.so`` (declared in ``include/fd_b200.h``).
+
+There is no CPU fallback: if the shared library is missing the import of this
+module fails loudly and nothing in the package can execute a time step.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
+
+FD_MAX_POINTS = 16
+FD_MAX_TERMS = 4
+FD_MAX_POST = 4
+FD_FLAG_INF = 0
+FD_FLAG_OVERRIDE = 1
+FD_NUM_FLAGS = 4
+
+# enum fd_ewise_op
+(OP_NEG, OP_ADD_FF, OP_SUB_FF, OP_MUL_FF, OP_DIV_FF, OP_POW_FF, OP_ADD_FS, OP_SUB_FS,
+ OP_MUL_FS, OP_DIV_FS, OP_POW_FS, OP_SQUARE, OP_RECIP, OP_SQRT, OP_COPY, OP_EULER) = range(16)
+
+# enum fd_post_op
+POST_MUL, POST_ADD, POST_SUB, POST_DIV, POST_NEG, POST_MUL_FIELD = range(6)
+
+
+class Stencil(C.Structure):
+    _fields_ = [("npts", C.c_int32),
+                ("shifts", C.c_int32 * FD_MAX_POINTS),
+                ("weights", C.c_double * FD_MAX_POINTS),
+                ("scale", C.c_double),
+                ("exact_div", C.c_int32)]
+
+
+class Term(C.Structure):
+    _fields_ = [("src", C.c_void_p),
+                ("axis", C.c_int32), ("periodic", C.c_int32),
+                ("lo", C.c_int32), ("hi", C.c_int32),
+                ("n_src", C.c_int32), ("subtract", C.c_int32),
+                ("has_pre", C.c_int32), ("negate", C.c_int32),
+                ("pre", C.c_double),
+                ("st", Stencil)]
+
+
+class Post(C.Structure):
+    _fields_ = [("op", C.c_int32), ("_pad", C.c_int32), ("s", C.c_double), ("coef", C.c_void_p)]
+
+
+class Fused(C.Structure):
+    _fields_ = [("n", C.c_int32 * 3),
+                ("nterms", C.c_int32),
+                ("term", Term * FD_MAX_TERMS),
+                ("npost", C.c_int32), ("depth", C.c_int32),
+                ("post", Post * FD_MAX_POST),
+                ("dt", C.c_double),
+                ("dot_out", C.c_void_p),
+                ("prev", C.c_void_p * 2),
+                ("out", C.c_void_p * 2),
+                ("face", ((C.c_void_p * 2) * 3) * 2),
+                ("nan_count", C.c_void_p * 2),
+                ("flags", C.c_void_p)]
+
+
+_I64, _P, _D, _I = C.c_int64, C.c_void_p, C.c_double, C.c_int
+
+# name -> (restype, argtypes); every symbol include/fd_b200.h declares
+SIGNATURES = {
+    "fd_abi_version": (C.c_int, []),
+    "fd_last_error": (C.c_char_p, []),
+    "fd_launch_count": (C.c_longlong, []),
+}
+for _sfx in ("f64", "f32"):
+    SIGNATURES.update({
+        f"fd_der_{_sfx}": (_I, [_P, _P, _I64, _I64, _I64, _I64, C.POINTER(Stencil), _I, _I64, _I64, _P, _P]),
+        f"fd_ewise_{_sfx}": (_I, [_I, _P, _P, _P, _D, _I64, _P]),
+        f"fd_merge_store_{_sfx}": (_I, [_P, _P, _I64, _P, _P, _P]),
+        f"fd_fill_{_sfx}": (_I, [_P, _D, _I64, _P]),
+        f"fd_face_store_{_sfx}": (_I, [_P, _P, _I64, _I64, _I64, _I64, _P]),
+        f"fd_count_nan_{_sfx}": (_I, [_P, _I64, _P, _P]),
+        f"fd_fused_step_{_sfx}": (_I, [C.POINTER(Fused), _P]),
+    })
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.isfile(LIB_PATH):
+        raise ImportError(
+            f"finite_difference (B200): {LIB_PATH} is missing. Build it with "
+            "`python -c 'import __graft_entry__ as g; g.build()'` from the repository root "
+            "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if lib.fd_abi_version() != 1:
+        raise ImportError(f"{LIB_PATH}: ABI version {lib.fd_abi_version()}, expected 1")
+    return lib
+
+
+lib = _load()
+
+
+def check(rc):
+    if rc != 0:
+        raise NativeError(lib.fd_last_error().decode())
+
+
+def suffix(dtype) -> str:
+    import numpy as np
+    return "f32" if np.dtype(dtype) == np.float32 else "f64"
+
+
+def fn(name, dtype):
+    return getattr(lib, f"{name}_{suffix(dtype)}")
+
+
+def make_stencil(shifts, weights, scale, exact_div=True) -> Stencil:
+    if len(shifts) > FD_MAX_POINTS:
+        raise NativeError(f"stencils with more than {FD_MAX_POINTS} points are not supported by the B200 kernels")
+    st = Stencil()
+    st.npts = len(shifts)
+    for i, (s, w) in enumerate(zip(shifts, weights)):
+        st.shifts[i] = int(s)
+        st.weights[i] = float(w)
+    st.scale = float(scale)
+    st.exact_div = 1 if exact_div else 0
+    return st

@@ -1,0 +1,207 @@
+/*
+ * fd_b200.h -- C ABI of libfd_b200.so: the B200 (sm_100a) kernels behind the
+ * time-stepping hot path of the `finite_difference` Python library.
+ *
+ * The reference (Ephraim-Bryski/Finite-Difference 0.0.3) has no FFI: its hot
+ * path is numpy code inside src/finite_difference/FD.py.  Each entry point
+ * below therefore cites the FD.py lines whose arithmetic it replaces; the
+ * Python package `finite_difference` (finite-difference_b200/) binds them
+ * with ctypes.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all data pointers are DEVICE pointers
+ *     owned by the caller unless stated otherwise; descriptor structs are
+ *     HOST pointers, read during the call only;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream);
+ *     every call is asynchronous on that stream;
+ *   - every function returns 0 on success, non-zero on error, and
+ *     fd_last_error() then describes the failure (thread-local string);
+ *   - dtype suffix: _f64 = IEEE double (the reference's only type),
+ *     _f32 = IEEE float (additive option);
+ *   - arithmetic mirrors numpy's order of operations exactly: products and
+ *     sums are separately rounded (no FMA contraction), stencil sums start
+ *     from 0.0 and accumulate in the user's point order;
+ *   - "unknown" is NaN, as in the reference (FD.py:310).
+ *
+ * Device-side conditions are reported through caller-owned device words:
+ *   flags[FD_FLAG_INF]      != 0  a der() produced +-inf        (FD.py:1112-1113)
+ *   flags[FD_FLAG_OVERRIDE] != 0  a known value hit a known one (FD.py:565-572)
+ * and NaN counters (one int64 per stored time level, FD.py:528-538).
+ */
+#ifndef FD_B200_H
+#define FD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FD_ABI_VERSION 1
+
+#define FD_MAX_POINTS 16 /* sample points per stencil                     */
+#define FD_MAX_TERMS 4   /* der() terms summed by one fused statement     */
+#define FD_MAX_POST 4    /* scalar/coefficient operations after the sum   */
+
+#define FD_FLAG_INF 0
+#define FD_FLAG_OVERRIDE 1
+#define FD_NUM_FLAGS 4
+
+/* One Stencil applied along one axis: integer index shifts (FD.py:1028-1044),
+ * the 2-decimal weights solved on the host (FD.py:938-951) and the divisor
+ * dx**der_order (FD.py:1107-1110).  Passed by value to the kernels, i.e. it
+ * lives in the constant bank for the duration of the launch. */
+typedef struct fd_stencil {
+  int32_t npts;
+  int32_t shifts[FD_MAX_POINTS];
+  double weights[FD_MAX_POINTS];
+  double scale;
+  int32_t exact_div; /* 1: divide (bit-exact); 0: multiply by 1/scale       */
+} fd_stencil_t;
+
+/* element-wise operations of FieldInstant arithmetic (FD.py:794-869) */
+enum fd_ewise_op {
+  FD_OP_NEG = 0,   /* dst = -a                                  FD.py:836 */
+  FD_OP_ADD_FF,    /* dst = a + b                               FD.py:839 */
+  FD_OP_SUB_FF,    /* dst = a - b                               FD.py:842 */
+  FD_OP_MUL_FF,    /* dst = a * b                               FD.py:845 */
+  FD_OP_DIV_FF,    /* dst = a / b                               FD.py:848 */
+  FD_OP_POW_FF,    /* dst = pow(a, b)                           FD.py:852 */
+  FD_OP_ADD_FS,    /* dst = a + s                               FD.py:839,856 */
+  FD_OP_SUB_FS,    /* dst = a - s  (also `s - a`, FD.py:859-860 quirk)    */
+  FD_OP_MUL_FS,    /* dst = a * s                               FD.py:845,862 */
+  FD_OP_DIV_FS,    /* dst = a / s                               FD.py:848 */
+  FD_OP_POW_FS,    /* dst = pow(a, s)                           FD.py:852 */
+  FD_OP_SQUARE,    /* dst = a * a   (numpy's a**2 fast path)              */
+  FD_OP_RECIP,     /* dst = 1 / a   (numpy's a**-1 fast path)             */
+  FD_OP_SQRT,      /* dst = sqrt(a) (numpy's a**0.5 fast path)            */
+  FD_OP_COPY,      /* dst = a       (numpy's a**1 fast path)              */
+  FD_OP_EULER      /* dst = a + b*s (two roundings)             FD.py:515-516 */
+};
+
+/* ---- library ------------------------------------------------------------ */
+
+/* ABI version of the loaded library (== FD_ABI_VERSION). No reference
+ * counterpart. */
+int fd_abi_version(void);
+
+/* Human-readable description of the last failure on this thread. */
+const char* fd_last_error(void);
+
+/* Number of kernels this library has launched since load (all threads);
+ * bench.py reports it as gpu_launches. */
+long long fd_launch_count(void);
+
+/* ---- unfused operators (any expression DAG, any number of dimensions) ---- */
+
+/* Stencil.der on one time slice viewed as (outer, n_src, inner) ->
+ * (outer, n_dst, inner), the derivative axis in the middle.
+ * periodic != 0: FD.py:1046-1055 (index wrap instead of np.roll copies),
+ *   n_dst must equal n_src.
+ * periodic == 0: FD.py:1058-1105; outputs with lo <= j < hi are computed from
+ *   src[j + shift_i], the others are NaN; n_dst = n_src + {-1, 0, +1}.
+ * Then / dx**order (FD.py:1107-1110) and the infinity flag (FD.py:1112). */
+int fd_der_f64(void* dst, const void* src, int64_t outer, int64_t n_src, int64_t n_dst,
+               int64_t inner, const fd_stencil_t* st, int periodic, int64_t lo, int64_t hi,
+               void* flags, void* stream);
+int fd_der_f32(void* dst, const void* src, int64_t outer, int64_t n_src, int64_t n_dst,
+               int64_t inner, const fd_stencil_t* st, int periodic, int64_t lo, int64_t hi,
+               void* flags, void* stream);
+
+/* FieldInstant arithmetic on n elements (FD.py:794-869); `b` is ignored by
+ * the field-scalar and unary forms, `s` by the field-field forms. dst may
+ * alias a or b. */
+int fd_ewise_f64(int op, void* dst, const void* a, const void* b, double s, int64_t n, void* stream);
+int fd_ewise_f32(int op, void* dst, const void* a, const void* b, double s, int64_t n, void* stream);
+
+/* Field.__set_data with allow_override=False (FD.py:541-576): merge the
+ * freshly computed slice `fresh` into the stored level `stored` (already
+ * holding NaN or boundary values): known fresh values are written (raising
+ * FD_FLAG_OVERRIDE if the stored one was known too), NaN fresh values keep
+ * what is stored.  `nan_count` (device int64*, may be NULL) is incremented by
+ * the number of NaNs left in `stored` (FD.py:528-529). */
+int fd_merge_store_f64(void* stored, const void* fresh, int64_t n, void* nan_count, void* flags, void* stream);
+int fd_merge_store_f32(void* stored, const void* fresh, int64_t n, void* nan_count, void* flags, void* stream);
+
+/* Fill n elements with `value` (NaN to make a level "unknown", FD.py:310). */
+int fd_fill_f64(void* dst, double value, int64_t n, void* stream);
+int fd_fill_f32(void* dst, double value, int64_t n, void* stream);
+
+/* Write one boundary face into a stored level viewed as (outer, n, inner):
+ * stored[o, index, i] = face[o, i] wherever face is known (set_BC with
+ * allow_override=True, FD.py:361-385 and 541-576). */
+int fd_face_store_f64(void* stored, const void* face, int64_t outer, int64_t n, int64_t inner, int64_t index, void* stream);
+int fd_face_store_f32(void* stored, const void* face, int64_t outer, int64_t n, int64_t inner, int64_t index, void* stream);
+
+/* Count NaNs of n elements into *nan_count (device int64*, incremented). */
+int fd_count_nan_f64(const void* src, int64_t n, void* nan_count, void* stream);
+int fd_count_nan_f32(const void* src, int64_t n, void* nan_count, void* stream);
+
+/* ---- fused statement: der terms + scalar arithmetic + Euler chain + BCs ---- */
+
+/* One der() term of the sum. The source slice has the target's dimensions
+ * except along `axis`, where it has n_src entries (staggered fixed axes differ
+ * by one). */
+typedef struct fd_term {
+  const void* src;
+  int32_t axis;      /* 0,1,2 in the collapsed (n0,n1,n2) view, n2 contiguous */
+  int32_t periodic;
+  int32_t lo, hi;    /* computed output range along axis when not periodic    */
+  int32_t n_src;
+  int32_t subtract;  /* 0: sum += term, 1: sum -= term (first term: ignored)   */
+  int32_t has_pre;   /* multiply the term by `pre` before summing (k*der(..))  */
+  int32_t negate;    /* unary minus on the term before summing                 */
+  double pre;
+  fd_stencil_t st;
+} fd_term_t;
+
+enum fd_post_op {
+  FD_POST_MUL = 0,  /* v = v * s        */
+  FD_POST_ADD,      /* v = v + s        */
+  FD_POST_SUB,      /* v = v - s        */
+  FD_POST_DIV,      /* v = v / s        */
+  FD_POST_NEG,      /* v = -v           */
+  FD_POST_MUL_FIELD /* v = v * coef[i]  (ConstantField.always, FD.py:759-762;
+                       the product is commutative so coef*v is identical) */
+};
+
+typedef struct fd_post {
+  int32_t op;
+  int32_t _pad;
+  double s;
+  const void* coef; /* FD_POST_MUL_FIELD: slice with the target's dimensions */
+} fd_post_t;
+
+/* `Field.dot...dot.assign_update(post(sum of terms))` followed by `depth`
+ * time_integrate_update calls up the .dot chain, executed in ONE pass:
+ *   rhs       = post(sum_k term_k)                   FD.py:990-1122, 794-869
+ *   dot_out   = rhs                     (optional)   FD.py:478-498
+ *   out[0]    = merge(prev[0] + rhs*dt,    faces[0]) FD.py:500-538, 541-576
+ *   out[1]    = merge(prev[1] + out[0]*dt, faces[1]) (depth == 2)
+ * Boundary faces hold the values the reference pre-populates at time t+1 with
+ * set_BC (FD.py:361-385); face[l][d][side] is an array over the two other
+ * dimensions in order, or NULL.  Periodic axes wrap the index in-kernel,
+ * fixed axes predicate on [lo, hi). */
+typedef struct fd_fused {
+  int32_t n[3];
+  int32_t nterms;
+  fd_term_t term[FD_MAX_TERMS];
+  int32_t npost;
+  int32_t depth;
+  fd_post_t post[FD_MAX_POST];
+  double dt;
+  void* dot_out;
+  const void* prev[2];
+  void* out[2];
+  const void* face[2][3][2];
+  void* nan_count[2]; /* device int64*, incremented by NaNs left in out[l]   */
+  void* flags;        /* device int64[FD_NUM_FLAGS]                          */
+} fd_fused_t;
+
+int fd_fused_step_f64(const fd_fused_t* desc, void* stream);
+int fd_fused_step_f32(const fd_fused_t* desc, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FD_B200_H */

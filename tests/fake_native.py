@@ -1,0 +1,249 @@
+"""TEST INFRASTRUCTURE ONLY: a numpy stand-in for ``libfd_b200.so`` and for the
+CUDA device, so that the *host-side* logic of the package (deferred DAG,
+pattern matcher, ring buffer bookkeeping, boundary-face extraction, history)
+can be exercised in the CPU-only container.  It is never imported by the
+package; the ``-m gpu`` tests run the same scenarios through the real library.
+
+"Device memory" is CPU torch tensors; the entry points read their arguments
+exactly as the C ABI declares them (addresses + sizes + descriptor structs)
+and compute with the oracle's numpy operations.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import contextlib
+
+import numpy as np
+import torch
+
+from oracle import fd_numpy as O
+
+
+def _arr(address, n, dtype=np.float64):
+    if n == 0:
+        return np.empty(0, dtype=dtype)
+    ctype = {np.dtype(np.float64): C.c_double, np.dtype(np.float32): C.c_float,
+             np.dtype(np.int64): C.c_int64}[np.dtype(dtype)]
+    return np.ctypeslib.as_array((ctype * int(n)).from_address(int(address)))
+
+
+def _val(p):
+    return p.value if hasattr(p, "value") else p
+
+
+class FakeLib:
+    """Subset of the C ABI in numpy, float64 only."""
+
+    def __init__(self):
+        self.launches = 0
+        self.error = b""
+
+    def fd_abi_version(self):
+        return 1
+
+    def fd_last_error(self):
+        return self.error
+
+    def fd_launch_count(self):
+        return self.launches
+
+    # -- helpers ------------------------------------------------------------
+    @staticmethod
+    def _stencil(st):
+        n = st.npts
+        return list(st.shifts[:n]), list(st.weights[:n]), st.scale
+
+    @staticmethod
+    def _der(src, axis, shifts, weights, scale, periodic, lo, hi, n_dst, flags):
+        if periodic:
+            out = np.zeros(src.shape)
+            for w, s in zip(weights, shifts):
+                out += w * np.roll(src, -s, axis=axis)
+        else:
+            shape = list(src.shape)
+            shape[axis] = n_dst
+            out = np.full(shape, np.nan)
+            part_shape = list(shape)
+            part_shape[axis] = hi - lo
+            part = np.zeros(part_shape)
+            sel = [slice(None)] * src.ndim
+            for w, s in zip(weights, shifts):
+                sel[axis] = slice(lo + s, hi + s)
+                part += w * src[tuple(sel)]
+            sel[axis] = slice(lo, hi)
+            out[tuple(sel)] = part
+        out = out / scale
+        if flags is not None and np.any(np.isinf(out)):
+            flags[0] = 1
+        return out
+
+    # -- unfused ------------------------------------------------------------
+    def fd_der_f64(self, dst, src, outer, n_src, n_dst, inner, st, periodic, lo, hi, flags, stream):
+        self.launches += 1
+        st = st._obj if hasattr(st, "_obj") else st.contents
+        shifts, weights, scale = self._stencil(st)
+        s = _arr(src, outer * n_src * inner).reshape(outer, n_src, inner)
+        f = _arr(flags, 4, np.int64) if flags else None
+        out = self._der(s, 1, shifts, weights, scale, periodic, lo, hi, n_dst, f)
+        _arr(dst, outer * n_dst * inner)[:] = out.reshape(-1)
+        return 0
+
+    def fd_ewise_f64(self, op, dst, a, b, s, n, stream):
+        self.launches += 1
+        x = np.array(_arr(a, n))
+        y = np.array(_arr(b, n)) if b else None
+        with np.errstate(all="ignore"):
+            r = {0: lambda: -x, 1: lambda: x + y, 2: lambda: x - y, 3: lambda: x * y, 4: lambda: x / y,
+                 5: lambda: x ** y, 6: lambda: x + s, 7: lambda: x - s, 8: lambda: x * s, 9: lambda: x / s,
+                 10: lambda: x ** s, 11: lambda: x * x, 12: lambda: 1 / x, 13: lambda: np.sqrt(x),
+                 14: lambda: x, 15: lambda: x + y * s}[op]()
+        _arr(dst, n)[:] = r
+        return 0
+
+    def fd_merge_store_f64(self, stored, fresh, n, nan_count, flags, stream):
+        self.launches += 1
+        st, fr = _arr(stored, n), _arr(fresh, n)
+        known = ~np.isnan(fr)
+        if np.any(~np.isnan(st[known])) and flags:
+            _arr(flags, 4, np.int64)[1] = 1
+        st[known] = fr[known]
+        if nan_count:
+            _arr(nan_count, 1, np.int64)[0] += int(np.isnan(st).sum())
+        return 0
+
+    def fd_fill_f64(self, dst, value, n, stream):
+        self.launches += 1
+        _arr(dst, n)[:] = value
+        return 0
+
+    def fd_face_store_f64(self, stored, face, outer, n, inner, index, stream):
+        self.launches += 1
+        st = _arr(stored, outer * n * inner).reshape(outer, n, inner)
+        fc = _arr(face, outer * inner).reshape(outer, inner)
+        known = ~np.isnan(fc)
+        st[:, index, :][known] = fc[known]
+        return 0
+
+    def fd_count_nan_f64(self, src, n, nan_count, stream):
+        self.launches += 1
+        _arr(nan_count, 1, np.int64)[0] += int(np.isnan(_arr(src, n)).sum())
+        return 0
+
+    # -- fused --------------------------------------------------------------
+    def fd_fused_step_f64(self, desc, stream):
+        self.launches += 1
+        d = desc._obj if hasattr(desc, "_obj") else desc.contents
+        n = tuple(d.n)
+        size = int(np.prod(n))
+        flags = _arr(d.flags, 4, np.int64) if d.flags else None
+        total = None
+        for k in range(d.nterms):
+            tm = d.term[k]
+            shifts, weights, scale = self._stencil(tm.st)
+            sshape = list(n)
+            sshape[tm.axis] = tm.n_src
+            src = _arr(tm.src, int(np.prod(sshape))).reshape(sshape)
+            v = self._der(src, tm.axis, shifts, weights, scale, tm.periodic, tm.lo, tm.hi, n[tm.axis], flags)
+            if tm.negate:
+                v = -v
+            if tm.has_pre:
+                v = v * tm.pre
+            total = v if k == 0 else (total - v if tm.subtract else total + v)
+        for k in range(d.npost):
+            po = d.post[k]
+            if po.op == 0:
+                total = total * po.s
+            elif po.op == 1:
+                total = total + po.s
+            elif po.op == 2:
+                total = total - po.s
+            elif po.op == 3:
+                total = total / po.s
+            elif po.op == 4:
+                total = -total
+            elif po.op == 5:
+                total = total * _arr(po.coef, size).reshape(n)
+        if d.dot_out:
+            _arr(d.dot_out, size)[:] = total.reshape(-1)
+        rate = total
+        for l in range(d.depth):
+            new = _arr(d.prev[l], size).reshape(n) + rate * d.dt
+            stored = np.full(n, np.nan)
+            for dim in range(3):
+                for side in range(2):
+                    fp = d.face[l][dim][side]
+                    if not fp:
+                        continue
+                    fshape = [n[a] for a in range(3) if a != dim]
+                    face = _arr(fp, int(np.prod(fshape))).reshape(fshape)
+                    sel = [slice(None)] * 3
+                    sel[dim] = 0 if side == 0 else n[dim] - 1
+                    tgt = stored[tuple(sel)]
+                    fill = np.isnan(tgt)
+                    tgt[fill] = face[fill]
+            known = ~np.isnan(new)
+            if flags is not None and np.any(~np.isnan(stored[known])):
+                flags[1] = 1
+            new[~known] = stored[~known]
+            _arr(d.out[l], size)[:] = new.reshape(-1)
+            if d.nan_count[l]:
+                _arr(d.nan_count[l], 1, np.int64)[0] += int(np.isnan(new).sum())
+            rate = new
+        return 0
+
+
+class FakeDevice:
+    index = 0
+
+    def __init__(self):
+        self.dev = torch.device("cpu")
+        self.copy_stream = None
+
+    stream = None
+    stream_ptr = 0
+
+    def synchronize(self):
+        pass
+
+    def empty(self, n, dtype):
+        return torch.empty(int(n), dtype=torch.float64)
+
+    def zeros_i64(self, n):
+        return torch.zeros(int(n), dtype=torch.int64)
+
+    def upload(self, array, dtype, out=None):
+        host = torch.from_numpy(np.ascontiguousarray(array, dtype=np.float64).reshape(-1).copy())
+        if out is None:
+            return host
+        out.copy_(host)
+        return out
+
+    def download(self, tensor, shape=None):
+        arr = tensor.numpy().copy()
+        return arr.reshape(shape) if shape is not None else arr
+
+    def pinned(self, shape, dtype):
+        buf = torch.empty(int(np.prod(shape)), dtype=torch.float64)
+        return buf, buf.numpy().reshape(shape)
+
+
+@contextlib.contextmanager
+def installed():
+    """Route the package's native calls and device plumbing to the fakes."""
+    import finite_difference._device as dev_mod
+    import finite_difference._engine as eng_mod
+    import finite_difference._native as nat
+
+    fake = FakeLib()
+    saved_fn, saved_get, saved_lib = nat.fn, dev_mod.Device.get, nat.lib
+    fake_dev = FakeDevice()
+    nat.fn = lambda name, dtype: getattr(fake, f"{name}_f64")
+    nat.lib = fake
+    dev_mod.Device.get = classmethod(lambda cls, index=None: fake_dev)
+    eng_mod.Device = dev_mod.Device
+    try:
+        yield fake
+    finally:
+        nat.fn, nat.lib = saved_fn, saved_lib
+        dev_mod.Device.get = saved_get

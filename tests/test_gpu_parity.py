@@ -1,0 +1,154 @@
+"""Parity tests proper (B200): the package, through the C ABI of
+libfd_b200.so, against the reference's golden outputs and the numpy oracle.
+fp64 results must be bit-identical (NaN pattern included)."""
+
+import contextlib
+import ctypes as C
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import fd_numpy as O
+from oracle import scenarios
+from tests.scenario_check import GOLD, run_and_compare
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fd():
+    import finite_difference as fd
+    return fd
+
+
+@pytest.mark.parametrize("name", sorted(scenarios.ALL))
+def test_scenario(fd, name):
+    run_and_compare(name, fd)
+
+
+@pytest.mark.parametrize("name", sorted(scenarios.ALL))
+def test_scenario_unfused_kernels(fd, name, monkeypatch):
+    monkeypatch.setenv("FD_B200_NO_FUSE", "1")
+    run_and_compare(name, fd)
+
+
+def test_der_cases_through_the_c_abi():
+    """fd_der_f64 called directly with plain pointers on the 120 golden cases."""
+    import torch
+    import finite_difference._native as nat
+    cases = json.load(open(os.path.join(GOLD, "der_cases.json")))
+    pack = np.load(os.path.join(GOLD, "der_cases.npz"))
+    flags = torch.zeros(nat.FD_NUM_FLAGS, dtype=torch.int64, device="cuda")
+    for i, c in enumerate(cases):
+        fe, te = c["kind"][0] == "e", c["kind"][1] == "e"
+        shifts, grow = O.stencil_shifts(c["points"], fe, te)
+        vin, want = pack[f"in{i}"], pack[f"out{i}"]
+        ax = c["axis"]
+        n_src = vin.shape[ax]
+        outer = int(np.prod(vin.shape[:ax])) if ax else 1
+        inner = int(np.prod(vin.shape[ax + 1:])) if ax + 1 < vin.ndim else 1
+        if c["periodic"]:
+            n_dst, lo, hi = n_src, 0, n_src
+        else:
+            n_dst = n_src + grow
+            guard = 1 if (fe and not te) else 0
+            lo = -min(int(shifts[0]), 0)
+            hi = lo + n_src + min(int(shifts[0]), 0) - max(int(shifts[-1]), guard)
+        st = nat.make_stencil(shifts, c["weights"], c["dx"] ** c["order"])
+        src = torch.from_numpy(vin.reshape(-1).copy()).cuda()
+        dst = torch.empty(outer * n_dst * inner, dtype=torch.float64, device="cuda")
+        nat.check(nat.lib.fd_der_f64(dst.data_ptr(), src.data_ptr(), outer, n_src, n_dst, inner, C.byref(st),
+                                     1 if c["periodic"] else 0, lo, hi, flags.data_ptr(), 0))
+        got = dst.cpu().numpy().reshape(want.shape)
+        assert np.array_equal(got, want, equal_nan=True), c
+    assert int(flags[nat.FD_FLAG_INF]) == 0
+
+
+def _heat(fd, shape, n_t, periodic, k, dt, ic, points=(-1, 0, 1), history="all"):
+    names = ["x", "y", "z"][:len(shape)]
+    axes = {"t": np.arange(n_t) * dt}
+    for n, a in zip(shape, names):
+        axes[a] = np.arange(n) * 1.0
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model(axes, "t", periodic=tuple(names) if periodic else (), history=history)
+        T = fd.Field(m, "T", n_time_ders=1)
+        d2 = fd.Stencil(list(points), 2)
+        T.set_IC_values(ic)
+        if not periodic:
+            for a in names:
+                T.set_BC("0", a, "start")
+                T.set_BC("0", a, "end")
+        while not m.finished:
+            acc = d2.der(T.prev, names[0])
+            for a in names[1:]:
+                acc = acc + d2.der(T.prev, a)
+            T.dot.assign_update(k * acc)
+            T.time_integrate_update()
+            m.increment_time()
+    return m, T
+
+
+@pytest.mark.parametrize("shape,periodic", [((67, 45, 130), True), ((33, 129, 70), False), ((1000, 37), False),
+                                            ((513, 300), True), ((5000,), True), ((3, 3, 3), True),
+                                            ((2, 2), False)])
+def test_heat_against_oracle_odd_shapes(fd, shape, periodic):
+    """Shapes that do not divide the thread-block tiles, both boundary kinds."""
+    ic = np.random.default_rng(11).random(shape)
+    m, T = _heat(fd, shape, 4, periodic, 0.1, 1e-3, ic)
+    want, want_dot = O.run_heat(shape, 4, periodic, 0.1, 1e-3, ic)
+    assert np.array_equal(T.data, want, equal_nan=True)
+    assert np.array_equal(T.dot.data, want_dot, equal_nan=True)
+    assert m._engine.stats["fused"] == 3 and m._engine.stats["unfused_statements"] == 0
+
+
+def test_wide_stencil_against_oracle(fd):
+    shape = (40, 52, 36)
+    ic = np.random.default_rng(12).random(shape)
+    m, T = _heat(fd, shape, 3, True, 0.05, 1e-3, ic, points=tuple(range(-4, 5)))
+    want, _ = O.run_heat(shape, 3, True, 0.05, 1e-3, ic, stencil_points=tuple(range(-4, 5)))
+    assert np.array_equal(T.data, want, equal_nan=True)
+
+
+def test_history_policies(fd):
+    shape = (20, 24, 28)
+    ic = np.random.default_rng(13).random(shape)
+    want, _ = O.run_heat(shape, 8, True, 0.1, 1e-3, ic)
+    _, T_last = _heat(fd, shape, 8, True, 0.1, 1e-3, ic, history="last")
+    got = T_last.data
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[-1], want[-1])
+    assert np.isnan(got[1:-1]).all()
+    _, T_k = _heat(fd, shape, 8, True, 0.1, 1e-3, ic, history=3)
+    got = T_k.data
+    for t in range(8):
+        if t % 3 == 0 or t == 7:
+            assert np.array_equal(got[t], want[t])
+        else:
+            assert np.isnan(got[t]).all()
+
+
+def test_instability_and_override_are_reported(fd):
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model({"t": np.arange(40) * 1.0, "x": np.arange(16) * 1e-3}, "t", periodic=("x",))
+        T = fd.Field(m, "T", n_time_ders=1)
+        d2 = fd.Stencil([-1, 0, 1], 2)
+        T.set_IC_values(np.random.default_rng(0).random(16) * 1e300)
+        with pytest.raises(Exception, match="Instability has led to infinite values"):
+            while not m.finished:
+                T.dot.assign_update(1e8 * d2.der(T.prev, "x"))
+                T.time_integrate_update()
+                m.increment_time()
+        # too many boundary conditions: BC on the derivative field as well
+        m = fd.Model({"t": np.arange(4) * 1.0, "x": np.arange(8) * 1.0}, "t")
+        u = fd.Field(m, "u", n_time_ders=1)
+        u.set_IC("x")
+        u.set_BC("0", "x", "start")
+        u.set_BC("0", "x", "end")
+        d1 = fd.Stencil([0, 1], 1)
+        with pytest.raises(Exception, match="attempting to override values"):
+            while not m.finished:
+                u.dot.assign_update(d1.der(u.prev, "x"))
+                u.time_integrate_update()
+                m.increment_time()
