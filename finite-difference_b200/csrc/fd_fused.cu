@@ -9,6 +9,8 @@
 //   inf check 1112-1113), arithmetic 794-869, assign_update 478-498,
 //   time_integrate_update 500-538, merge 541-576.
 
+#include <stdlib.h>
+
 #include "fd_fused.cuh"
 
 namespace fdb {
@@ -65,11 +67,26 @@ fused_kernel(const __grid_constant__ DevFused<T> P) {
 }
 
 template <typename T>
+int try_star(const DevFused<T>& F, cudaStream_t stream);  // fd_star.cu
+
+static bool star_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("FD_B200_NO_STAR");
+    return !(v && v[0] == '1');
+  }();
+  return on;
+}
+
+template <typename T>
 static int fused_impl(const fd_fused_t* d, void* stream) {
   DevFused<T> P;
   if (make_dev_fused<T>(d, &P)) return 1;
   const int n0 = P.n[0], n1 = P.n[1], n2 = P.n[2];
   if ((int64_t)n0 * n1 * n2 == 0) return 0;
+  if (star_enabled()) {
+    const int r = try_star<T>(P, (cudaStream_t)stream);
+    if (r != 0) return r < 0 ? 1 : 0;
+  }
   // threads along the contiguous axis first; 256 threads per block
   int bx = 32;
   while (bx < 128 && bx < n2) bx <<= 1;

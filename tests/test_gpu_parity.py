@@ -152,3 +152,22 @@ def test_instability_and_override_are_reported(fd):
                 u.dot.assign_update(d1.der(u.prev, "x"))
                 u.time_integrate_update()
                 m.increment_time()
+
+
+def test_general_fused_kernel_without_star_specialisation():
+    """FD_B200_NO_STAR=1 (read once per process) forces the general fused
+    kernel for statements the star kernel would otherwise take."""
+    import subprocess
+    import sys
+    code = (
+        "import sys, os; sys.path[:0] = [%r, %r]\n"
+        "import finite_difference as fd\n"
+        "from tests.scenario_check import run_and_compare\n"
+        "for name in ['readme_1d','heat2d_fixed','heat3d_periodic','heat3d_fixed','wave2d','heat2d_time_middle','variable_coefficient']:\n"
+        "    run_and_compare(name, fd)\n"
+        "print('ok')\n"
+    ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+         os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "finite-difference_b200"))
+    env = dict(os.environ, FD_B200_NO_STAR="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stdout + out.stderr
