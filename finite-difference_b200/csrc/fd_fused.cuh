@@ -139,7 +139,7 @@ __device__ __forceinline__ T apply_post(const DevFused<T>& P, T v, int64_t idx) 
 // Value the reference pre-populated at time t+1 on the boundary faces (set_BC),
 // NaN when the point is on no registered face.
 template <typename T>
-__device__ __forceinline__ T stored_face_value(const DevFused<T>& P, int l, int i0, int i1, int i2) {
+__device__ __noinline__ T stored_face_value(const DevFused<T>& P, int l, int i0, int i1, int i2) {
   const int n0 = P.n[0], n1 = P.n[1], n2 = P.n[2];
   T v = quiet_nan<T>();
   const T* f;

@@ -48,6 +48,12 @@ class Model:
 {non_axes_periodic} is/are not"
 
         self.axes = axes
+        # derived axis facts are fixed after construction; the reference
+        # recomputes them on every access (FD.py:243-258), which costs O(axis
+        # length) Python work per call and would dominate large-grid steps
+        self._names = list(axes.keys())
+        self._lengths = [len(v) for v in axes.values()]
+        self._steps = [v[1] - v[0] for v in axes.values()]
         self.periodic = periodic
         self.time_step = 0
         self.time_axis = time_axis
@@ -119,11 +125,11 @@ class Model:
 
     @property
     def axes_lengths(self):
-        return [len(list(axis_range)) for axis_range in self.axes.values()]
+        return list(self._lengths)
 
     @property
     def axes_names(self):
-        return list(self.axes.keys())
+        return list(self._names)
 
     @property
     def axes_values(self):
@@ -131,7 +137,7 @@ class Model:
 
     @property
     def axes_step_size(self):
-        return [axis_range[1] - axis_range[0] for axis_range in self.axes.values()]
+        return list(self._steps)
 
     def interact(self):
         """
