@@ -120,9 +120,12 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------- the B200 model
-def build_model(fd, workload, n_t, ic, history="last"):
-    """The workload written against the public API (what a user script does)."""
+def build_model(fd, workload, n_t, ic, history="last", world=1):
+    """The workload written against the public API (what a user script does).
+    With several ranks the grid grows along the slowest axis (weak scaling):
+    every rank holds one `shape`-sized slab and passes it as its initial values."""
     shape = WORKLOADS[workload][1]
+    shape = (shape[0] * world,) + tuple(shape[1:])
     names = ["x", "y", "z"][:len(shape)]
     axes = {"t": np.arange(n_t) * DT}
     for n, a in zip(shape, names):
@@ -249,7 +252,7 @@ def run_b200(args):
     pinned = torch.empty(int(points), dtype=torch.float64, pin_memory=True)
     ic = pinned.numpy().reshape(shape)
     ic[...] = np.random.default_rng(rank).random(shape)
-    m, F, step = build_model(fd, args.workload, W + K + 2, ic)
+    m, F, step = build_model(fd, args.workload, W + K + 2, ic, world=world)
     for _ in range(W):
         step()
     m.synchronize()
@@ -280,10 +283,10 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
-    m2, F2, step2 = build_model(fd, args.workload, K + 1, ic)
+    m2, F2, step2 = build_model(fd, args.workload, K + 1, ic, world=world)
     for _ in range(K):
         step2()
-    final = F2.data_level(K)
+    final = F2.local_level(K)
     m2.synchronize()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
@@ -308,7 +311,8 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": desc, "grid_per_gpu": "x".join(map(str, shape)),
                    "l2": "inputs larger than L2 (state level = %.0f MiB vs 126 MB L2)" % (points * 8 / 2 ** 20),
-                   "multi_gpu": "replicas (no halo exchange yet)" if world > 1 else "single GPU",
+                   "multi_gpu": (f"slab decomposition along x over {world} ranks, NCCL send/recv halo exchange every step"
+                                 if world > 1 else "single GPU"),
                    "history": "last", "engine_stats": stats},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(args.workload), "peak_source": peak_src,

@@ -21,11 +21,15 @@ fused_kernel(const __grid_constant__ DevFused<T> P) {
   const int n0 = P.n[0], n1 = P.n[1], n2 = P.n[2];
   const int i2 = blockIdx.x * blockDim.x + threadIdx.x;
   const int i1 = blockIdx.y * blockDim.y + threadIdx.y;
-  const bool active = (i2 < n2) && (i1 < n1);
+  bool active = (i2 < n2) && (i1 < n1);
+  if (P.range_dim == 2) active = active && i2 >= P.range_begin && i2 < P.range_end;
+  if (P.range_dim == 1) active = active && i1 >= P.range_begin && i1 < P.range_end;
+  const int x_lo = P.range_dim == 0 ? P.range_begin : 0;
+  const int x_hi = P.range_dim == 0 ? P.range_end : n0;
   unsigned nan_cnt[2] = {0u, 0u};
   bool saw_inf = false, clash = false;
 
-  for (int i0 = blockIdx.z * P.x_chunk, i0_end = min(i0 + P.x_chunk, n0); i0 < i0_end; ++i0) {
+  for (int i0 = x_lo + blockIdx.z * P.x_chunk, i0_end = min(i0 + P.x_chunk, x_hi); i0 < i0_end; ++i0) {
     if (!active) continue;
     T total = (T)0;
     for (int k = 0; k < P.nterms; ++k) {
@@ -96,11 +100,13 @@ static int fused_impl(const fd_fused_t* d, void* stream) {
   int64_t gy = (n1 + by - 1) / by;
   if (gy > 65535) return fail("fd_fused_step: middle dimension %d too large", n1);
   // consecutive planes handled by one block: reuses neighbour planes through L1
+  const int nx = P.range_dim == 0 ? P.range_end - P.range_begin : n0;   // planes actually processed
+  if (nx <= 0) return 0;
   int chunk = 8;
-  while (chunk > 1 && (int64_t)((n2 + bx - 1) / bx) * gy * ((n0 + chunk - 1) / chunk) < 148 * 8) chunk >>= 1;
-  while ((n0 + chunk - 1) / chunk > 65535) chunk <<= 1;
+  while (chunk > 1 && (int64_t)((n2 + bx - 1) / bx) * gy * ((nx + chunk - 1) / chunk) < 148 * 8) chunk >>= 1;
+  while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.x_chunk = chunk;
-  dim3 grid((n2 + bx - 1) / bx, (unsigned)gy, (n0 + chunk - 1) / chunk);
+  dim3 grid((n2 + bx - 1) / bx, (unsigned)gy, (nx + chunk - 1) / chunk);
   fused_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(P);
   return check_launch("fd_fused_step");
 }

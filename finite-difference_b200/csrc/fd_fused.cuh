@@ -36,6 +36,8 @@ struct DevFused {
   const T* face[2][3][2];
   long long* nan_count[2];
   long long* flags;
+  int32_t range_dim, range_begin, range_end;
+  int32_t rim_lo[3], rim_hi[3];
 };
 
 template <typename T>
@@ -117,6 +119,25 @@ inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P) {
       }
   }
   P->flags = (long long*)d->flags;
+  P->range_dim = d->range_dim;
+  P->range_begin = d->range_begin;
+  P->range_end = d->range_end;
+  if (d->range_dim > 2) return fail("fd_fused_step: range_dim %d", d->range_dim);
+  if (d->range_dim >= 0) {
+    if (d->range_begin < 0 || d->range_end > d->n[d->range_dim] || d->range_begin > d->range_end)
+      return fail("fd_fused_step: range [%d,%d) outside dimension %d of %d points", d->range_begin, d->range_end,
+                  d->range_dim, d->n[d->range_dim]);
+  } else {
+    P->range_dim = -1;
+    P->range_begin = 0;
+    P->range_end = 0;
+  }
+  for (int a = 0; a < 3; ++a) {
+    P->rim_lo[a] = d->rim_lo[a];
+    P->rim_hi[a] = d->rim_hi[a];
+    if (d->rim_lo[a] < 0 || d->rim_hi[a] >= d->n[a] + (d->n[a] == 0))
+      return fail("fd_fused_step: rim indices of dimension %d outside the slice", a);
+  }
   return 0;
 }
 
@@ -140,15 +161,15 @@ __device__ __forceinline__ T apply_post(const DevFused<T>& P, T v, int64_t idx) 
 // NaN when the point is on no registered face.
 template <typename T>
 __device__ __noinline__ T stored_face_value(const DevFused<T>& P, int l, int i0, int i1, int i2) {
-  const int n0 = P.n[0], n1 = P.n[1], n2 = P.n[2];
+  const int n1 = P.n[1], n2 = P.n[2];
   T v = quiet_nan<T>();
   const T* f;
-  if (i2 == 0 && (f = P.face[l][2][0])) v = f[(int64_t)i0 * n1 + i1];
-  if (i2 == n2 - 1 && (f = P.face[l][2][1]) && is_nan(v)) v = f[(int64_t)i0 * n1 + i1];
-  if (i1 == 0 && (f = P.face[l][1][0]) && is_nan(v)) v = f[(int64_t)i0 * n2 + i2];
-  if (i1 == n1 - 1 && (f = P.face[l][1][1]) && is_nan(v)) v = f[(int64_t)i0 * n2 + i2];
-  if (i0 == 0 && (f = P.face[l][0][0]) && is_nan(v)) v = f[(int64_t)i1 * n2 + i2];
-  if (i0 == n0 - 1 && (f = P.face[l][0][1]) && is_nan(v)) v = f[(int64_t)i1 * n2 + i2];
+  if (i2 == P.rim_lo[2] && (f = P.face[l][2][0])) v = f[(int64_t)i0 * n1 + i1];
+  if (i2 == P.rim_hi[2] && (f = P.face[l][2][1]) && is_nan(v)) v = f[(int64_t)i0 * n1 + i1];
+  if (i1 == P.rim_lo[1] && (f = P.face[l][1][0]) && is_nan(v)) v = f[(int64_t)i0 * n2 + i2];
+  if (i1 == P.rim_hi[1] && (f = P.face[l][1][1]) && is_nan(v)) v = f[(int64_t)i0 * n2 + i2];
+  if (i0 == P.rim_lo[0] && (f = P.face[l][0][0]) && is_nan(v)) v = f[(int64_t)i1 * n2 + i2];
+  if (i0 == P.rim_hi[0] && (f = P.face[l][0][1]) && is_nan(v)) v = f[(int64_t)i1 * n2 + i2];
   return v;
 }
 
@@ -158,9 +179,9 @@ __device__ __forceinline__ void fused_epilogue(const DevFused<T>& P, T rhs, int6
                                                int i2, unsigned (&nan_cnt)[2], bool& clash) {
   if (P.dot_out) P.dot_out[idx] = rhs;
   const int fm = P.any_face;  // bit d: some level has a face on dimension d
-  const bool rim = fm && (((fm & 4) && (i2 == 0 || i2 == P.n[2] - 1)) ||
-                          ((fm & 2) && (i1 == 0 || i1 == P.n[1] - 1)) ||
-                          ((fm & 1) && (i0 == 0 || i0 == P.n[0] - 1)));
+  const bool rim = fm && (((fm & 4) && (i2 == P.rim_lo[2] || i2 == P.rim_hi[2])) ||
+                          ((fm & 2) && (i1 == P.rim_lo[1] || i1 == P.rim_hi[1])) ||
+                          ((fm & 1) && (i0 == P.rim_lo[0] || i0 == P.rim_hi[0])));
   T rate = rhs;
 #pragma unroll
   for (int l = 0; l < 2; ++l) {

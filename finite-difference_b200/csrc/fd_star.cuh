@@ -81,7 +81,8 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
   const int vstride = blockDim.x;
   const int vz = blockIdx.x * (blockDim.x * VPT) + threadIdx.x;   // first vector of this thread
   const int i1 = blockIdx.y * blockDim.y + threadIdx.y;
-  const bool active = (vz + (VPT - 1) * vstride < nvec) && (i1 < n1);
+  bool active = (vz + (VPT - 1) * vstride < nvec) && (i1 < n1);
+  if (F.range_dim == 1) active = active && i1 >= F.range_begin && i1 < F.range_end;
   const int i2 = vz * VN;
   const int estride = vstride * VN;       // elements between a thread's vectors
 
@@ -92,8 +93,10 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
   unsigned nan_cnt[2] = {0u, 0u};
   bool saw_inf = false, clash = false;
 
-  const int x_begin = blockIdx.z * P.x_chunk;
-  const int x_end = min(x_begin + P.x_chunk, n0);
+  const int x_lo = F.range_dim == 0 ? F.range_begin : 0;
+  const int x_hi = F.range_dim == 0 ? F.range_end : n0;
+  const int x_begin = x_lo + blockIdx.z * P.x_chunk;
+  const int x_end = min(x_begin + P.x_chunk, x_hi);
   const int plane = n1 * n2;               // elements; the host guarantees < 2^31
 
   auto load_row = [estride](const T* p) {
@@ -151,8 +154,8 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
     }
     const bool ybad = BOUNDED && HY && !ay.periodic && (i1 < ay.lo || i1 >= ay.hi);
     const int fm = BOUNDED ? F.any_face : 0;
-    const bool rim_y = (fm & 2) && (i1 == 0 || i1 == n1 - 1);
-    const bool rim_z = (fm & 4) && (i2 == 0 || i2 + (VPT - 1) * estride + VN == n2);
+    const bool rim_y = (fm & 2) && (i1 == F.rim_lo[1] || i1 == F.rim_hi[1]);
+    const bool rim_z = (fm & 4) && (i2 <= F.rim_lo[2] || i2 + (VPT - 1) * estride + VN > F.rim_hi[2]);
 
     int64_t idx0 = ((int64_t)x_begin * n1 + i1) * n2 + i2;
     // running pointers: one 64-bit add per iteration instead of re-deriving
@@ -260,7 +263,7 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
 
       // epilogue on vectors: optional .dot store, Euler chain, boundary merge
       if (F.dot_out) store_row(F.dot_out + idx0, rhs);
-      const bool rim_row = rim_y || ((fm & 1) && (i0 == 0 || i0 == n0 - 1));
+      const bool rim_row = rim_y || ((fm & 1) && (i0 == F.rim_lo[0] || i0 == F.rim_hi[0]));
       Row rate = rhs;
 #pragma unroll
       for (int l = 0; l < 2; ++l) {
@@ -278,7 +281,7 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
           for (int e = 0; e < TE; ++e) {
             T v = nv.v[e];
             const int j2 = i2 + (e / VN) * estride + e % VN;
-            if (BOUNDED && (rim_row || (rim_z && (j2 == 0 || j2 == n2 - 1)))) {
+            if (BOUNDED && (rim_row || (rim_z && (j2 == F.rim_lo[2] || j2 == F.rim_hi[2])))) {
               const T stored = stored_face_value(F, l, i0, i1, j2);
               if (is_nan(v))
                 v = stored;
@@ -332,7 +335,9 @@ inline int tuning_chunk() {
 template <typename T, int R, int AXES, int MODE, int VPT>
 static void launch_star_vpt(StarParams<T>& P, int bx, int by, cudaStream_t stream) {
   constexpr int VN = Vec<T>::N;
-  const int n0 = P.F.n[0], n1 = P.F.n[1], nvec = P.F.n[2] / VN;
+  const int n1 = P.F.n[1], nvec = P.F.n[2] / VN;
+  const int n0 = P.F.range_dim == 0 ? P.F.range_end - P.F.range_begin : P.F.n[0];   // planes processed
+  if (n0 <= 0) return;
   const int gx = (nvec + bx * VPT - 1) / (bx * VPT), gy = (n1 + by - 1) / by;
   // planes marched by one block: long enough to amortise the 2R+1 preloaded
   // planes, short enough to give every SM several blocks

@@ -82,7 +82,12 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
           F.face[l][1][sd] = nullptr;
         }
       F.any_face = (F.any_face & 4) | ((F.any_face & 2) ? 1 : 0);
+      F.rim_lo[0] = F.rim_lo[1];
+      F.rim_hi[0] = F.rim_hi[1];
+      F.rim_lo[1] = F.rim_hi[1] = 0;
+      if (F.range_dim == 1) F.range_dim = 0;
     }
+    if (F.range_dim == 2) return false;   // sub-ranges along the vectorised axis: general kernel
   }
   if (F.nterms < 1 || F.nterms > 3) return false;
   const DevTerm<T>& t0 = F.term[0];

@@ -97,15 +97,36 @@ class Device:
         arr = tensor.detach().cpu().numpy()
         return arr.reshape(shape) if shape is not None else arr
 
-    def pinned(self, shape, dtype):
-        """Pinned host ndarray (falls back to pageable if pinning fails)."""
+    # -- pinned host memory for snapshots --------------------------------------
+    ARENA_BYTES = 8 << 20
+
+    def pinned(self, n, dtype):
+        """Flat pinned host tensor of ``n`` elements.  Small requests are carved
+        out of 8 MiB arenas (one cudaHostAlloc per arena, not per time level);
+        the arena lives as long as any view of it does."""
         t = torch()
-        n = int(np.prod(shape)) if len(shape) else 1
+        td = _torch_dtype(dtype)
+        nbytes = int(n) * np.dtype(dtype).itemsize
+        if nbytes >= self.ARENA_BYTES // 4:
+            return self._host_alloc(int(n), td)
+        arena = getattr(self, "_arena", None)
+        if arena is None or arena[2] != td or arena[1] + int(n) > arena[0].numel():
+            arena = [self._host_alloc(self.ARENA_BYTES // np.dtype(dtype).itemsize, td), 0, td]
+            self._arena = arena
+        view = arena[0][arena[1]:arena[1] + int(n)]
+        arena[1] += (int(n) + 31) // 32 * 32          # keep views 256-byte aligned
+        return view
+
+    @staticmethod
+    def _host_alloc(n, td):
+        t = torch()
         try:
-            buf = t.empty(n, dtype=_torch_dtype(dtype), pin_memory=True)
-        except RuntimeError:
-            buf = t.empty(n, dtype=_torch_dtype(dtype))
-        return buf, buf.numpy().reshape(shape)
+            return t.empty(n, dtype=td, pin_memory=True)
+        except RuntimeError:                             # pinning refused: pageable still works
+            return t.empty(n, dtype=td)
+
+    def event(self):
+        return torch().cuda.Event()
 
 
 def ptr(tensor):

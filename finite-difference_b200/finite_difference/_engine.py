@@ -44,18 +44,26 @@ class FieldState:
         from .field import ConstantField
         self.field = field
         self.engine = engine
-        self.size = int(np.prod(field._slice_shape)) if field._slice_shape else 1
+        self.size = int(np.prod(field._slice_shape)) if field._slice_shape else 1   # owned elements
         self.constant = isinstance(field, ConstantField)
         self.integrated = field.dot is not None
         depth = 2 if self.integrated else 1
-        self.ring = [engine.dev.empty(self.size, engine.dtype) for _ in range(depth)]
+        # slab decomposition: [H ghost planes | owned planes | H ghost planes]
+        self.H = engine.H
+        shape = tuple(field._slice_shape)
+        self.owned0 = shape[0] if shape else 1
+        self.plane = self.size // self.owned0 if self.owned0 else 0
+        self.ext_shape = ((self.owned0 + 2 * self.H,) + shape[1:]) if self.H else shape
+        self.ext_size = self.size + 2 * self.H * self.plane
+        self.ring = [engine.dev.empty(self.ext_size, engine.dtype) for _ in range(depth)]
         self.held = [-1] * depth          # time index each slot holds
+        self.halo_ok = [False] * depth    # ghost planes of the slot are current
         self.saved = set()                # time indices already in the host history
         self.faces = None                 # {(dim, side): (tensor, per_time_elems or 0)}
         self.counts = engine.dev.zeros_i64(engine.n_t) if self.integrated else None
         self.counts_checked = engine.model.time_step
         s = len(field._slice_shape)
-        self.dims3 = (1,) * (3 - s) + tuple(field._slice_shape) if s <= 3 else None
+        self.dims3 = (1,) * (3 - s) + tuple(self.ext_shape) if s <= 3 else None
         if self.constant:
             self.load_level(0)
         elif self.integrated:
@@ -71,13 +79,14 @@ class FieldState:
         if level is None:
             level = self.field._hist.read({eng.model.time_axis: t})
         k = self.slot_index(t)
-        eng.dev.upload(level, eng.dtype, out=self.ring[k])
+        eng.dev.upload(level, eng.dtype, out=self.owned(self.ring[k]))
         self.held[k] = t
+        self.halo_ok[k] = False
         self.saved.add(t)
         if self.counts is not None:      # NaN count of the level, on the device (FD.py:528)
             self.counts[t] = 0
-            nat.check(eng._fn["fd_count_nan"](ptr(self.ring[k]), self.size, self.counts.data_ptr() + 8 * t,
-                                              eng.stream))
+            nat.check(eng._fn["fd_count_nan"](ptr(self.owned(self.ring[k])), self.size,
+                                              self.counts.data_ptr() + 8 * t, eng.stream))
 
     def level(self, t):
         k = self.slot_index(t)
@@ -94,7 +103,22 @@ class FieldState:
         k = self.slot_index(t)
         self.engine.wait_for_copies(self, k)
         self.held[k] = t
+        self.halo_ok[k] = False
         return self.ring[k]
+
+    def owned(self, tensor):
+        """The owned planes of an extended level (all of it without ghosts)."""
+        if not self.H:
+            return tensor
+        return tensor[self.H * self.plane:self.H * self.plane + self.size]
+
+    def refresh_ghosts(self, t):
+        """Halo exchange for time level ``t`` (no-op when already current)."""
+        k = 0 if self.constant else self.slot_index(t)
+        if self.H and not self.halo_ok[k]:
+            self.engine.slab.exchange(self.ring[k], self.plane, self.owned0, self.H)
+            self.halo_ok[k] = True
+            self.engine.stats["halo_exchanges"] = self.engine.stats.get("halo_exchanges", 0) + 1
 
     # -- boundary faces ------------------------------------------------------
     def build_faces(self):
@@ -108,12 +132,21 @@ class FieldState:
             if f._hist.time_dependent({axis: idx}, t_from):
                 full = f._hist.read({axis: idx})
                 free = [a for a in model.axes_names if a != axis]
-                full = np.moveaxis(full, free.index(model.time_axis), 0)
+                full = self._pad_face(np.moveaxis(full, free.index(model.time_axis), 0), dim, 1)
                 per = int(np.prod(full.shape[1:])) if full.ndim > 1 else 1
                 self.faces[(dim, side)] = (eng.dev.upload(full, eng.dtype), per)
             else:
-                face = f._hist.read({axis: idx, model.time_axis: t_from})
+                face = self._pad_face(f._hist.read({axis: idx, model.time_axis: t_from}), dim, 0)
                 self.faces[(dim, side)] = (eng.dev.upload(face, eng.dtype), 0)
+
+    def _pad_face(self, face, dim, lead):
+        """Faces of the other axes span the slab axis: give them the ghost planes
+        of the extended layout (NaN = nothing stored there)."""
+        if not self.H or dim == 0:
+            return face
+        pad = [(0, 0)] * face.ndim
+        pad[lead] = (self.H, self.H)
+        return np.pad(face, pad, constant_values=np.nan)
 
     def face_ptr(self, dim, side, t):
         if self.faces is None:
@@ -138,6 +171,8 @@ class Engine:
         self.n_t = len(model.axes[model.time_axis])
         self.flags = self.dev.zeros_i64(nat.FD_NUM_FLAGS)
         self.states = {}
+        self.slab = model._slab
+        self.H = None if self.slab is not None else 0     # ghost depth, fixed at the first executed step
         self.exact_div = os.environ.get("FD_B200_FAST_SCALE", "0") != "1"
         self.fuse = os.environ.get("FD_B200_NO_FUSE", "0") != "1"
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
@@ -154,6 +189,8 @@ class Engine:
     def state(self, field):
         st = self.states.get(id(field))
         if st is None:
+            if self.H is None:
+                raise Exception("on several GPUs expression values can only be read after the first time step")
             st = self.states[id(field)] = FieldState(self, field)
         return st
 
@@ -172,6 +209,11 @@ class Engine:
     # --------------------------------------------------------------- execute
     def execute(self, stmts):
         t = self.model.time_step
+        if self.H is None:
+            self.H = _slab_reach(stmts)
+            if self.H > min(self.slab.counts):
+                raise Exception(f"stencils reach {self.H} planes along {self.slab.axis}, more than the "
+                                f"{min(self.slab.counts)} planes of the smallest slab")
         for f in self.model.fields:          # initial levels go up before the first launch
             self.state(f)
         reads_new = set()
@@ -248,8 +290,15 @@ class Engine:
             tm = d.term[k]
             tm.src = src.data_ptr()
             tm.axis = der.axis + pad
-            tm.periodic = 1 if der.periodic else 0
-            tm.lo, tm.hi, tm.n_src = der.lo, der.hi, der.n_src
+            if der.slab:
+                # the slab is a non-periodic window of the global axis; ghosts hold the neighbours' planes
+                src_state.refresh_ghosts(leaf.t)
+                tm.periodic = 0
+                tm.lo, tm.hi = self._local_range(der, dot_state.owned0)
+                tm.n_src = src_state.ext_shape[0]
+            else:
+                tm.periodic = 1 if der.periodic else 0
+                tm.lo, tm.hi, tm.n_src = der.lo, der.hi, der.n_src
             tm.subtract = 1 if subtract else 0
             tm.has_pre = 0 if pre is None else 1
             tm.pre = 0.0 if pre is None else pre
@@ -279,8 +328,29 @@ class Engine:
             for (dim, side), _ in ls.face_items():
                 d.face[l][dim + pad][side] = ls.face_ptr(dim, side, t + 1)
         d.flags = self.flags.data_ptr()
+        d.range_dim = -1
+        for a in range(3):
+            d.rim_lo[a], d.rim_hi[a] = 0, max(dims3[a] - 1, 0)
+        if self.H:
+            # only the owned planes are computed; the domain faces of the slab
+            # axis sit on the first / last owned plane of the end ranks
+            d.range_dim, d.range_begin, d.range_end = pad, self.H, self.H + dot_state.owned0
+            d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
         nat.check(self._fn["fd_fused_step"](C.byref(d), self.stream))
         return True
+
+    def _local_range(self, der, owned_out):
+        """[lo, hi) of a der along the slab axis in extended local plane indices:
+        the global range (FD.py:1073-1105) cut to the planes this rank owns."""
+        reach = max(abs(s) for s in der.shifts)
+        if reach > self.H:
+            raise Exception(f"a stencil reaches {reach} planes along the decomposed axis {self.slab.axis}, but the "
+                            f"slabs were laid out with {self.H} ghost planes (the reach seen in the first time step)")
+        lo_g, hi_g = (0, der.n_dst) if der.periodic else (der.lo, der.hi)
+        first = self.slab.lo
+        lo = max(lo_g, first) - first + self.H
+        hi = min(hi_g, first + owned_out) - first + self.H
+        return lo, max(hi, lo)
 
     # --------------------------------------------------------- unfused path
     def _eval(self, node, memo):
@@ -288,10 +358,12 @@ class Engine:
         got = memo.get(id(node))
         if got is not None:
             return got
-        n = int(np.prod(node.shape)) if node.shape else 1
+        n = self._ext_elems(node.shape)
         if isinstance(node, Leaf):
             out = self.state(node.field).level(node.t)
         elif isinstance(node, Const):
+            if self.H:
+                raise Exception("user-built FieldInstant arrays are not supported on several GPUs")
             out = self.dev.upload(node.array, self.dtype)
         elif isinstance(node, Unary):
             a = self._eval(node.a, memo)
@@ -301,18 +373,34 @@ class Engine:
             out = self._eval_binary(node, n, memo)
         elif isinstance(node, Der):
             a = self._eval(node.a, memo)
-            shape = node.a.shape
+            shape = self._ext_shape(node.a.shape)
             outer = int(np.prod(shape[:node.axis])) if node.axis else 1
             inner = int(np.prod(shape[node.axis + 1:])) if node.axis + 1 < len(shape) else 1
             st = nat.make_stencil(node.shifts, node.weights, node.scale, self.exact_div)
             out = self.dev.empty(n, self.dtype)
-            nat.check(self._fn["fd_der"](ptr(out), ptr(a), outer, node.n_src, node.n_dst, inner, C.byref(st),
-                                          1 if node.periodic else 0, node.lo, node.hi, ptr(self.flags),
-                                          self.stream))
+            n_src, n_dst, periodic, lo, hi = node.n_src, node.n_dst, node.periodic, node.lo, node.hi
+            if node.slab:
+                if not isinstance(node.a, Leaf):
+                    raise NotImplementedError(
+                        "on several GPUs a derivative along the decomposed axis must be taken of a stored "
+                        "field level (prev/new/always), not of an intermediate expression")
+                self.state(node.a.field).refresh_ghosts(node.a.t)
+                n_src, n_dst, periodic = shape[0], node.shape[0] + 2 * self.H, False
+                lo, hi = self._local_range(node, node.shape[0])
+            nat.check(self._fn["fd_der"](ptr(out), ptr(a), outer, n_src, n_dst, inner, C.byref(st),
+                                          1 if periodic else 0, lo, hi, ptr(self.flags), self.stream))
         else:
             raise TypeError(f"unknown expression node {type(node).__name__}")
         memo[id(node)] = out
         return out
+
+    def _ext_shape(self, shape):
+        shape = tuple(shape)
+        return ((shape[0] + 2 * self.H,) + shape[1:]) if (self.H and shape) else shape
+
+    def _ext_elems(self, shape):
+        shape = self._ext_shape(shape)
+        return int(np.prod(shape)) if shape else 1
 
     def _eval_binary(self, node, n, memo):
         out = self.dev.empty(n, self.dtype)
@@ -336,12 +424,14 @@ class Engine:
         """Claim the slot for level t and give it the reference's pre-populated
         content: NaN plus the boundary faces of that time (FD.py:310, 361-385)."""
         slot = st.claim(t)
-        nat.check(self._fn["fd_fill"](ptr(slot), float("nan"), st.size, self.stream))
-        shape = st.field._slice_shape
+        nat.check(self._fn["fd_fill"](ptr(slot), float("nan"), st.ext_size, self.stream))
+        shape = st.ext_shape
         for (dim, side), _ in st.face_items():
             outer = int(np.prod(shape[:dim])) if dim else 1
             inner = int(np.prod(shape[dim + 1:])) if dim + 1 < len(shape) else 1
             index = 0 if side == 0 else shape[dim] - 1
+            if dim == 0 and st.H:
+                index = st.H if side == 0 else st.H + st.owned0 - 1
             nat.check(self._fn["fd_face_store"](ptr(slot), st.face_ptr(dim, side, t), outer, shape[dim], inner,
                                                  index, self.stream))
         return slot
@@ -352,35 +442,80 @@ class Engine:
         st = self.state(field)
         fresh = self._eval(node, memo)
         slot = self._prefilled(st, t + 1)
-        nat.check(self._fn["fd_merge_store"](ptr(slot), ptr(fresh), st.size, 0, ptr(self.flags), self.stream))
+        nat.check(self._fn["fd_merge_store"](ptr(st.owned(slot)), ptr(st.owned(fresh)), st.size, 0,
+                                              ptr(self.flags), self.stream))
 
     def _generic_integrate(self, field, t):
         st, dot = self.state(field), self.state(field.dot)
-        fresh = self.dev.empty(st.size, self.dtype)
+        fresh = self.dev.empty(st.ext_size, self.dtype)
         nat.check(self._fn["fd_ewise"](nat.OP_EULER, ptr(fresh), ptr(st.level(t)), ptr(dot.level(t + 1)),
-                                        float(self.model.dt), st.size, self.stream))
+                                        float(self.model.dt), st.ext_size, self.stream))
         slot = self._prefilled(st, t + 1)
-        nat.check(self._fn["fd_merge_store"](ptr(slot), ptr(fresh), st.size, st.counts.data_ptr() + 8 * (t + 1),
-                                              ptr(self.flags), self.stream))
+        nat.check(self._fn["fd_merge_store"](ptr(st.owned(slot)), ptr(st.owned(fresh)), st.size,
+                                              st.counts.data_ptr() + 8 * (t + 1), ptr(self.flags), self.stream))
 
     # ------------------------------------------------------ host interaction
     def evaluate_to_host(self, node):
         out = self._eval(node, {})
+        if self.H:
+            plane = int(np.prod(node.shape[1:])) if len(node.shape) > 1 else 1
+            out = out[self.H * plane:(self.H + node.shape[0]) * plane]
         arr = self.dev.download(out, node.shape)
         self.poll(final=True)
         return np.array(arr, dtype=np.float64)
 
     def snapshot(self, st, t):
-        """Device level -> host history."""
+        """Device level -> pinned host memory, asynchronously on the copy stream.
+
+        The compute stream only records an event; the copy stream waits for it,
+        copies the ring slot into pinned memory and records a second event that
+        the compute stream waits on before it overwrites that slot again
+        (``wait_for_copies``)."""
         k = st.slot_index(t)
         if t in st.saved or st.held[k] != t:
             return
-        arr = self.dev.download(st.ring[k], st.field._slice_shape)
-        st.field._hist.write_level(t, np.array(arr, dtype=np.float64))
         st.saved.add(t)
+        host = self.dev.pinned(st.size, self.dtype)
+        if self.dev.copy_stream is None:              # CPU stand-in used by the host-logic tests
+            host.copy_(st.owned(st.ring[k]))
+            self.pending_copies.append((st, k, t, host, None))
+            return
+        tc = self.dev
+        import torch
+        ready = tc.event()
+        ready.record(tc.stream)
+        with torch.cuda.stream(tc.copy_stream):
+            tc.copy_stream.wait_event(ready)
+            host.copy_(st.owned(st.ring[k]), non_blocking=True)
+            done = tc.event()
+            done.record(tc.copy_stream)
+        self.pending_copies.append((st, k, t, host, done))
+        if len(self.pending_copies) > 64:
+            self.drain_copies(keep=32)
 
     def wait_for_copies(self, st, slot):
-        return
+        """The compute stream must not overwrite a ring slot that is still being
+        copied out."""
+        for (pst, k, _, _, done) in self.pending_copies:
+            if pst is st and k == slot and done is not None:
+                self.dev.stream.wait_event(done)
+
+    def drain_copies(self, field=None, keep=0):
+        """Hand finished (or, with keep=0, all) snapshot copies to the host history."""
+        rest = []
+        n = len(self.pending_copies)
+        for i, item in enumerate(self.pending_copies):
+            st, k, t, host, done = item
+            if (field is not None and st.field is not field) or i >= n - keep:
+                rest.append(item)
+                continue
+            if done is not None:
+                done.synchronize()
+            arr = host.numpy().reshape(st.field._slice_shape)
+            if arr.dtype != np.float64:
+                arr = arr.astype(np.float64)
+            st.field._hist.write_level(t, arr)
+        self.pending_copies = rest
 
     def sync_history(self, field):
         """Bring ``Field.data`` up to date: outstanding copies plus the level the
@@ -389,6 +524,7 @@ class Engine:
         if st is None or st.constant:
             return
         self.snapshot(st, self.model.time_step)
+        self.drain_copies(field)
         self.poll(final=True)
 
     def host_changed(self, field):
@@ -410,6 +546,8 @@ class Engine:
         if now == self.last_poll and not final:
             return
         self.last_poll = now
+        if self.slab is not None:            # every rank polls at the same steps
+            self.slab.all_reduce(self.flags, "max")
         flags = self.flags.cpu().numpy()    # synchronises the compute stream
         if flags[nat.FD_FLAG_INF] or flags[nat.FD_FLAG_OVERRIDE]:
             self.flags.zero_()
@@ -421,7 +559,10 @@ class Engine:
         for st in self.states.values():
             if st.counts is None or st.counts_checked >= now:
                 continue
-            counts = st.counts[st.counts_checked:now + 1].cpu().numpy()
+            window = st.counts[st.counts_checked:now + 1]
+            if self.slab is not None:
+                window = self.slab.all_reduce(window.clone(), "sum")
+            counts = window.cpu().numpy()
             first = st.counts_checked
             st.counts_checked = now
             for k in range(1, len(counts)):
@@ -430,6 +571,29 @@ class Engine:
                     print(LOSING_MSG)
                     self.model.insufficient_bc = True
                     return
+
+
+def _slab_reach(stmts):
+    """Largest stencil reach along the decomposed axis over the recorded statements."""
+    reach = 0
+
+    def walk(node):
+        nonlocal reach
+        if isinstance(node, Der):
+            if node.slab:
+                reach = max(reach, max(abs(s) for s in node.shifts))
+            walk(node.a)
+        elif isinstance(node, Unary):
+            walk(node.a)
+        elif isinstance(node, Binary):
+            for side in (node.a, node.b):
+                if isinstance(side, Node):
+                    walk(side)
+
+    for _, _, node in stmts:
+        if node is not None:
+            walk(node)
+    return reach
 
 
 def _collect_new_reads(node, t_new, out):

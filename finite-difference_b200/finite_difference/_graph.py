@@ -66,7 +66,8 @@ class Binary(Node):
 class Der(Node):
     """``stencil.der(a, axis)`` (FD.py:990-1122) with everything the kernels
     need resolved at record time."""
-    __slots__ = ("a", "axis", "shifts", "weights", "scale", "periodic", "lo", "hi", "n_src", "n_dst", "stencil")
+    __slots__ = ("a", "axis", "shifts", "weights", "scale", "periodic", "lo", "hi", "n_src", "n_dst", "stencil",
+                 "slab")
 
     def __init__(self, a, shape, axis, shifts, weights, scale, periodic, lo, hi, n_src, n_dst, stencil):
         super().__init__(shape)
@@ -74,6 +75,7 @@ class Der(Node):
         self.shifts, self.weights, self.scale = tuple(int(s) for s in shifts), tuple(weights), scale
         self.periodic, self.lo, self.hi, self.n_src, self.n_dst = periodic, lo, hi, n_src, n_dst
         self.stencil = stencil
+        self.slab = False   # True: along the axis that is decomposed over ranks
 
     def key(self):
         return ("der", self.axis, self.shifts, self.weights, float(self.scale), self.periodic, self.a.key())

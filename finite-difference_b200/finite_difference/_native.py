@@ -12,6 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
 
+ABI_VERSION = 2
 FD_MAX_POINTS = 16
 FD_MAX_TERMS = 4
 FD_MAX_POST = 4
@@ -61,7 +62,9 @@ class Fused(C.Structure):
                 ("out", C.c_void_p * 2),
                 ("face", ((C.c_void_p * 2) * 3) * 2),
                 ("nan_count", C.c_void_p * 2),
-                ("flags", C.c_void_p)]
+                ("flags", C.c_void_p),
+                ("range_dim", C.c_int32), ("range_begin", C.c_int32), ("range_end", C.c_int32),
+                ("rim_lo", C.c_int32 * 3), ("rim_hi", C.c_int32 * 3)]
 
 
 _I64, _P, _D, _I = C.c_int64, C.c_void_p, C.c_double, C.c_int
@@ -99,8 +102,8 @@ def _load():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.restype = res
         fn.argtypes = args
-    if lib.fd_abi_version() != 1:
-        raise ImportError(f"{LIB_PATH}: ABI version {lib.fd_abi_version()}, expected 1")
+    if lib.fd_abi_version() != ABI_VERSION:
+        raise ImportError(f"{LIB_PATH}: ABI version {lib.fd_abi_version()}, expected {ABI_VERSION}")
     return lib
 
 

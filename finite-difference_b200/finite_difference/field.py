@@ -56,6 +56,12 @@ class Field:
         self.edge_axes = edge_axes
         self.updated = False
         self.IC_set = False
+        self._global_shape = tuple(lengths.values())
+        slab = model._slab
+        if slab is not None:
+            # this rank holds one slab of the slowest spatial axis (see _dist.py)
+            self._slab_extra = slab.axis in edge_axes and slab.axis not in model.periodic
+            lengths[slab.axis] = slab.owned(self._slab_extra)
         self._shape = tuple(lengths.values())
         self._slice_shape = tuple(n for a, n in lengths.items() if a != model.time_axis)
         self._hist = HostHistory(model.axes_names, self._shape, model.time_axis)
@@ -69,6 +75,9 @@ class Field:
         unknown (FD.py:310).  Levels the history policy did not keep read as
         the reference's pre-populated content (NaN plus boundary values)."""
         self.model._sync_history(self)
+        slab = self.model._slab
+        if slab is not None:
+            return slab.gather_arrays(self._hist.materialise(), self.model._names.index(slab.axis))
         return self._hist.materialise()
 
     @data.setter
@@ -83,6 +92,17 @@ class Field:
         """Additive to the reference API: one time level as a host array, without
         assembling the dense history (``Field.data`` of a 512^3 x 100-step run
         would need 100 GiB).  Levels the history policy skipped read as NaN."""
+        t = int(t) + (self._shape[self.model.axes_names.index(self.model.time_axis)] if t < 0 else 0)
+        level = self.local_level(t)
+        slab = self.model._slab
+        if slab is not None:
+            space = [a for a in self.model._names if a != self.model.time_axis]
+            return slab.gather_arrays(level, space.index(slab.axis))
+        return level
+
+    def local_level(self, t):
+        """Additive: like ``data_level`` but only this rank's slab when the model
+        is decomposed over several GPUs (no communication)."""
         t = int(t) + (self._shape[self.model.axes_names.index(self.model.time_axis)] if t < 0 else 0)
         self.model._sync_history(self)
         level = self._hist.direct_level(t)
@@ -144,6 +164,10 @@ instead first use the assign_update method and then use the new property"
         array is used as is -- pass a view of pinned memory for fast upload."""
         assert self.dot != None, "field must have a time derivative to set initial conditions"
         values = np.asarray(values)
+        slab = self.model._slab
+        if slab is not None and values.shape != self._slice_shape:
+            # a global array: keep this rank's slab (the slab axis is the first spatial axis)
+            values = values[slab.lo:slab.lo + self._slice_shape[0]]
         assert values.shape == self._slice_shape, f"initial values must have shape {self._slice_shape}"
         self._hist.write({self.model.time_axis: 0}, values, copy=False)
         self.model._host_changed(self)
@@ -174,6 +198,12 @@ instead first use the assign_update method and then use the new property"
         assert type(expression) == str, "expression must be a string"
         assert type(location) == dict
         model = self.model
+        slab = model._slab
+        if slab is not None and slab.axis in location:
+            # a face of the decomposed axis belongs to the first / last rank only
+            if not (slab.first if location[slab.axis] == 0 else slab.last):
+                self._check_index(location)
+                return
         steps = dict(zip(model.axes_names, model.axes_step_size))
         free, coords = [], []
         for name, values in zip(model.axes_names, model.axes_values):
@@ -185,6 +215,8 @@ instead first use the assign_update method and then use the new property"
                 values = [v - dx / 2 for v in values]
                 if name not in model.periodic:
                     values.append(values[-1] + dx)
+            if slab is not None and name == slab.axis:
+                values = values[slab.lo:slab.lo + self._shape[model._names.index(name)]]
             free.append(name)
             coords.append(values)
         values = _expr.evaluate(expression, model.axes_names, free, coords)

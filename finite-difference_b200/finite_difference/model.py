@@ -70,6 +70,8 @@ class Model:
         self.history = history
         self._pending = []       # statements recorded in the current step
         self._engine = None      # created at the first executed statement
+        from ._dist import make_slab
+        self._slab = make_slab(self)   # None unless this process is one rank of several
 
     # ---- reference API -----------------------------------------------------
     def check_IC(self):

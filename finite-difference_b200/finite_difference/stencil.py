@@ -118,6 +118,11 @@ class Stencil:
         src_shape = f._node.shape
         n_src = src_shape[axis_n]
         periodic = der_axis in model.periodic
+        slab = model._slab
+        along_slab = slab is not None and der_axis == slab.axis
+        if along_slab:
+            # ranges are worked out on the GLOBAL axis; the engine maps them to the slab
+            n_src = slab.n + (1 if (on_edges and not periodic) else 0)
         if periodic:
             n_dst, lo, hi = n_src, 0, n_src
         else:
@@ -141,6 +146,9 @@ class Stencil:
                         "stencil sample points must be sorted ascending on a fixed axis")
         out_shape = list(src_shape)
         out_shape[axis_n] = n_dst
+        if along_slab:
+            lands_on_edges = stencil.to_edge if stencil.from_edge != stencil.to_edge else on_edges
+            out_shape[axis_n] = slab.owned(lands_on_edges and not periodic)
 
         dx = dict(zip(model.axes_names, model.axes_step_size))[der_axis]
         scale = dx ** stencil.der_order            # may be np.int64, like the reference
@@ -153,5 +161,6 @@ class Stencil:
 
         node = Der(f._node, out_shape, axis_n, shifts, stencil.weights, scale, periodic, int(lo), int(hi),
                    int(n_src), int(n_dst), stencil)
+        node.slab = along_slab
         out = FieldInstant(model, edges, f.name, node)
         return out

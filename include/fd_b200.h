@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define FD_ABI_VERSION 1
+#define FD_ABI_VERSION 2
 
 #define FD_MAX_POINTS 16 /* sample points per stencil                     */
 #define FD_MAX_TERMS 4   /* der() terms summed by one fused statement     */
@@ -181,7 +181,11 @@ typedef struct fd_post {
  * Boundary faces hold the values the reference pre-populates at time t+1 with
  * set_BC (FD.py:361-385); face[l][d][side] is an array over the two other
  * dimensions in order, or NULL.  Periodic axes wrap the index in-kernel,
- * fixed axes predicate on [lo, hi). */
+ * fixed axes predicate on [lo, hi).
+ * Multi-GPU: a slab carries ghost planes along its decomposed dimension; the
+ * caller exchanges them (NCCL send/recv), describes that dimension as
+ * non-periodic with [lo, hi) = the planes it owns and restricts execution
+ * with range_dim / range_begin / range_end. */
 typedef struct fd_fused {
   int32_t n[3];
   int32_t nterms;
@@ -196,6 +200,13 @@ typedef struct fd_fused {
   const void* face[2][3][2];
   void* nan_count[2]; /* device int64*, incremented by NaNs left in out[l]   */
   void* flags;        /* device int64[FD_NUM_FLAGS]                          */
+  /* Sub-range execution (slab decomposition, boundary/interior split): only
+   * points with range_begin <= index[range_dim] < range_end are computed and
+   * stored; range_dim < 0 means the whole slice.  With ghost planes around a
+   * slab the domain faces do not sit at index 0 / n-1: rim_lo[d] / rim_hi[d]
+   * give the index along d where face[l][d][0] / face[l][d][1] apply. */
+  int32_t range_dim, range_begin, range_end;
+  int32_t rim_lo[3], rim_hi[3];
 } fd_fused_t;
 
 int fd_fused_step_f64(const fd_fused_t* desc, void* stream);

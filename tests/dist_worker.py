@@ -1,0 +1,49 @@
+"""One rank of the slab-decomposition tests (spawned by test_dist_gloo.py on
+the CPU with gloo + the numpy stand-in for the native library, and by
+test_gpu_dist.py on GPUs with NCCL + the real library).
+
+usage: python tests/dist_worker.py <backend> <scenario> [<scenario> ...]
+Environment: RANK, WORLD_SIZE, MASTER_ADDR, MASTER_PORT (torch.distributed).
+"""
+
+import contextlib
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "finite-difference_b200")]
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def main():
+    backend, names = sys.argv[1], sys.argv[2:]
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    if backend == "nccl":
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)) % torch.cuda.device_count())
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    else:
+        dist.init_process_group("gloo")
+    import finite_difference as fd
+    from tests.scenario_check import run_and_compare
+
+    ctx = contextlib.nullcontext()
+    if backend == "gloo":
+        from tests import fake_native
+        ctx = fake_native.installed()
+    with ctx:
+        for name in names:
+            results = run_and_compare(name, fd, check_prints=False)
+            assert results
+    # every rank must have seen a decomposed model
+    m = fd.Model({"t": [0, 1], "x": np.arange(4 * world) * 1.0}, "t")
+    assert m._slab is not None and m._slab.world == world
+    dist.barrier()
+    dist.destroy_process_group()
+    print(f"rank {rank}/{world} ok: {len(names)} scenarios")
+
+
+if __name__ == "__main__":
+    main()

@@ -40,7 +40,7 @@ class FakeLib:
         self.error = b""
 
     def fd_abi_version(self):
-        return 1
+        return 2
 
     def fd_last_error(self):
         return self.error
@@ -164,8 +164,12 @@ class FakeLib:
                 total = -total
             elif po.op == 5:
                 total = total * _arr(po.coef, size).reshape(n)
+        region = [slice(None)] * 3
+        if d.range_dim >= 0:
+            region[d.range_dim] = slice(d.range_begin, d.range_end)
+        region = tuple(region)
         if d.dot_out:
-            _arr(d.dot_out, size)[:] = total.reshape(-1)
+            _arr(d.dot_out, size).reshape(n)[region] = total[region]
         rate = total
         for l in range(d.depth):
             new = _arr(d.prev[l], size).reshape(n) + rate * d.dt
@@ -178,17 +182,18 @@ class FakeLib:
                     fshape = [n[a] for a in range(3) if a != dim]
                     face = _arr(fp, int(np.prod(fshape))).reshape(fshape)
                     sel = [slice(None)] * 3
-                    sel[dim] = 0 if side == 0 else n[dim] - 1
+                    sel[dim] = d.rim_lo[dim] if side == 0 else d.rim_hi[dim]
                     tgt = stored[tuple(sel)]
                     fill = np.isnan(tgt)
                     tgt[fill] = face[fill]
             known = ~np.isnan(new)
-            if flags is not None and np.any(~np.isnan(stored[known])):
+            if flags is not None and np.any(~np.isnan(stored[region][known[region]])):
                 flags[1] = 1
             new[~known] = stored[~known]
-            _arr(d.out[l], size)[:] = new.reshape(-1)
+            out = _arr(d.out[l], size).reshape(n)
+            out[region] = new[region]
             if d.nan_count[l]:
-                _arr(d.nan_count[l], 1, np.int64)[0] += int(np.isnan(new).sum())
+                _arr(d.nan_count[l], 1, np.int64)[0] += int(np.isnan(new[region]).sum())
             rate = new
         return 0
 
@@ -223,9 +228,8 @@ class FakeDevice:
         arr = tensor.numpy().copy()
         return arr.reshape(shape) if shape is not None else arr
 
-    def pinned(self, shape, dtype):
-        buf = torch.empty(int(np.prod(shape)), dtype=torch.float64)
-        return buf, buf.numpy().reshape(shape)
+    def pinned(self, n, dtype):
+        return torch.empty(int(n), dtype=torch.float64)
 
 
 @contextlib.contextmanager

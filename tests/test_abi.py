@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     for name in names:
         assert hasattr(lib, name), f"{name} declared in fd_b200.h but not exported"
         assert name in nat.SIGNATURES, f"{name} has no ctypes signature in _native.py"
-    assert lib.fd_abi_version() == 1
+    assert lib.fd_abi_version() == nat.ABI_VERSION
     assert set(nat.SIGNATURES) == set(names)
 
 

@@ -1,0 +1,29 @@
+"""Slab decomposition on real GPUs (NCCL halo exchange over NVLink): needs at
+least two devices, so it is skipped on the single-GPU box and run with
+`gpurun --gpus 2 -- python -m pytest tests/test_gpu_dist.py -m gpu`."""
+
+import pytest
+
+from tests.test_dist_gloo import SCENARIOS, launch
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_slab_decomposition_nccl(world):
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    names = [n for n in SCENARIOS if not (world == 4 and n in ("acoustic3d_fixed", "heat4d_periodic", "heat3d_periodic",
+                                                               "heat3d_fixed", "acoustic3d"))]
+    launch(world, "nccl", names)
+
+
+def test_slab_decomposition_nccl_unfused():
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    launch(2, "nccl", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d"], {"FD_B200_NO_FUSE": "1"})
