@@ -18,14 +18,11 @@ namespace fdb {
 template <typename T>
 __global__ void __launch_bounds__(256)
 fused_kernel(const __grid_constant__ DevFused<T> P) {
-  const int n0 = P.n[0], n1 = P.n[1], n2 = P.n[2];
+  const int n1 = P.n[1], n2 = P.n[2];
   const int i2 = blockIdx.x * blockDim.x + threadIdx.x;
   const int i1 = blockIdx.y * blockDim.y + threadIdx.y;
-  bool active = (i2 < n2) && (i1 < n1);
-  if (P.range_dim == 2) active = active && i2 >= P.range_begin && i2 < P.range_end;
-  if (P.range_dim == 1) active = active && i1 >= P.range_begin && i1 < P.range_end;
-  const int x_lo = P.range_dim == 0 ? P.range_begin : 0;
-  const int x_hi = P.range_dim == 0 ? P.range_end : n0;
+  const bool active = i2 >= P.box_lo[2] && i2 < P.box_hi[2] && i1 >= P.box_lo[1] && i1 < P.box_hi[1];
+  const int x_lo = P.box_lo[0], x_hi = P.box_hi[0];
   unsigned nan_cnt[2] = {0u, 0u};
   bool saw_inf = false, clash = false;
 
@@ -100,7 +97,8 @@ static int fused_impl(const fd_fused_t* d, void* stream) {
   int64_t gy = (n1 + by - 1) / by;
   if (gy > 65535) return fail("fd_fused_step: middle dimension %d too large", n1);
   // consecutive planes handled by one block: reuses neighbour planes through L1
-  const int nx = P.range_dim == 0 ? P.range_end - P.range_begin : n0;   // planes actually processed
+  const int nx = P.box_hi[0] - P.box_lo[0];   // planes actually processed
+  if (P.box_hi[1] <= P.box_lo[1] || P.box_hi[2] <= P.box_lo[2]) return 0;
   if (nx <= 0) return 0;
   int chunk = 8;
   while (chunk > 1 && (int64_t)((n2 + bx - 1) / bx) * gy * ((nx + chunk - 1) / chunk) < 148 * 8) chunk >>= 1;

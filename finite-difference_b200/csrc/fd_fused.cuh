@@ -36,7 +36,8 @@ struct DevFused {
   const T* face[2][3][2];
   long long* nan_count[2];
   long long* flags;
-  int32_t range_dim, range_begin, range_end;
+  int32_t box_lo[3], box_hi[3];
+  int32_t whole;   // the box is the whole slice
   int32_t rim_lo[3], rim_hi[3];
 };
 
@@ -119,18 +120,16 @@ inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P) {
       }
   }
   P->flags = (long long*)d->flags;
-  P->range_dim = d->range_dim;
-  P->range_begin = d->range_begin;
-  P->range_end = d->range_end;
-  if (d->range_dim > 2) return fail("fd_fused_step: range_dim %d", d->range_dim);
-  if (d->range_dim >= 0) {
-    if (d->range_begin < 0 || d->range_end > d->n[d->range_dim] || d->range_begin > d->range_end)
-      return fail("fd_fused_step: range [%d,%d) outside dimension %d of %d points", d->range_begin, d->range_end,
-                  d->range_dim, d->n[d->range_dim]);
-  } else {
-    P->range_dim = -1;
-    P->range_begin = 0;
-    P->range_end = 0;
+  const bool no_box = d->box_hi[0] == 0 && d->box_hi[1] == 0 && d->box_hi[2] == 0 && d->box_lo[0] == 0 &&
+                      d->box_lo[1] == 0 && d->box_lo[2] == 0;
+  P->whole = 1;
+  for (int a = 0; a < 3; ++a) {
+    P->box_lo[a] = no_box ? 0 : d->box_lo[a];
+    P->box_hi[a] = no_box ? d->n[a] : d->box_hi[a];
+    if (P->box_lo[a] < 0 || P->box_hi[a] > d->n[a] || P->box_lo[a] > P->box_hi[a])
+      return fail("fd_fused_step: box [%d,%d) outside dimension %d of %d points", P->box_lo[a], P->box_hi[a], a,
+                  d->n[a]);
+    if (P->box_lo[a] != 0 || P->box_hi[a] != d->n[a]) P->whole = 0;
   }
   for (int a = 0; a < 3; ++a) {
     P->rim_lo[a] = d->rim_lo[a];

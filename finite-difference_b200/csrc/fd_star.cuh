@@ -79,10 +79,9 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
   // thread sits blockDim.x vectors after vector v-1, so every load instruction
   // of a warp reads one contiguous 512-byte run
   const int vstride = blockDim.x;
-  const int vz = blockIdx.x * (blockDim.x * VPT) + threadIdx.x;   // first vector of this thread
-  const int i1 = blockIdx.y * blockDim.y + threadIdx.y;
-  bool active = (vz + (VPT - 1) * vstride < nvec) && (i1 < n1);
-  if (F.range_dim == 1) active = active && i1 >= F.range_begin && i1 < F.range_end;
+  const int vz = F.box_lo[2] / VN + blockIdx.x * (blockDim.x * VPT) + threadIdx.x;   // first vector of this thread
+  const int i1 = F.box_lo[1] + blockIdx.y * blockDim.y + threadIdx.y;
+  const bool active = (vz + (VPT - 1) * vstride < F.box_hi[2] / VN) && (i1 < F.box_hi[1]);
   const int i2 = vz * VN;
   const int estride = vstride * VN;       // elements between a thread's vectors
 
@@ -93,8 +92,7 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
   unsigned nan_cnt[2] = {0u, 0u};
   bool saw_inf = false, clash = false;
 
-  const int x_lo = F.range_dim == 0 ? F.range_begin : 0;
-  const int x_hi = F.range_dim == 0 ? F.range_end : n0;
+  const int x_lo = F.box_lo[0], x_hi = F.box_hi[0];
   const int x_begin = x_lo + blockIdx.z * P.x_chunk;
   const int x_end = min(x_begin + P.x_chunk, x_hi);
   const int plane = n1 * n2;               // elements; the host guarantees < 2^31
@@ -335,9 +333,10 @@ inline int tuning_chunk() {
 template <typename T, int R, int AXES, int MODE, int VPT>
 static void launch_star_vpt(StarParams<T>& P, int bx, int by, cudaStream_t stream) {
   constexpr int VN = Vec<T>::N;
-  const int n1 = P.F.n[1], nvec = P.F.n[2] / VN;
-  const int n0 = P.F.range_dim == 0 ? P.F.range_end - P.F.range_begin : P.F.n[0];   // planes processed
-  if (n0 <= 0) return;
+  // extents of the box being processed
+  const int n0 = P.F.box_hi[0] - P.F.box_lo[0], n1 = P.F.box_hi[1] - P.F.box_lo[1];
+  const int nvec = (P.F.box_hi[2] - P.F.box_lo[2]) / VN;
+  if (n0 <= 0 || n1 <= 0 || nvec <= 0) return;
   const int gx = (nvec + bx * VPT - 1) / (bx * VPT), gy = (n1 + by - 1) / by;
   // planes marched by one block: long enough to amortise the 2R+1 preloaded
   // planes, short enough to give every SM several blocks
@@ -353,7 +352,7 @@ static void launch_star_vpt(StarParams<T>& P, int bx, int by, cudaStream_t strea
 template <typename T, int R, int AXES, int MODE>
 static void launch_star(StarParams<T>& P, cudaStream_t stream) {
   constexpr int VN = Vec<T>::N;
-  const int n1 = P.F.n[1], nvec = P.F.n[2] / VN;
+  const int n1 = P.F.box_hi[1] - P.F.box_lo[1], nvec = (P.F.box_hi[2] - P.F.box_lo[2]) / VN;
   int by = 1;                            // rows per block
   while (by < 8 && by < n1) by <<= 1;
   int bx = 256 / by;                     // threads along the contiguous axis

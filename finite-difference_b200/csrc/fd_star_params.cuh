@@ -85,9 +85,13 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
       F.rim_lo[0] = F.rim_lo[1];
       F.rim_hi[0] = F.rim_hi[1];
       F.rim_lo[1] = F.rim_hi[1] = 0;
-      if (F.range_dim == 1) F.range_dim = 0;
+      F.box_lo[0] = F.box_lo[1];
+      F.box_hi[0] = F.box_hi[1];
+      F.box_lo[1] = 0;
+      F.box_hi[1] = 1;
     }
-    if (F.range_dim == 2) return false;   // sub-ranges along the vectorised axis: general kernel
+    // sub-ranges along the vectorised axis must fall on 128-bit vector boundaries
+    if (F.box_lo[2] % VN != 0 || (F.box_hi[2] % VN != 0 && F.box_hi[2] != F.n[2])) return false;
   }
   if (F.nterms < 1 || F.nterms > 3) return false;
   const DevTerm<T>& t0 = F.term[0];
@@ -160,9 +164,19 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
   for (int l = 0; l < 2; ++l) P->prev_is_src[l] = (l < F.depth && F.prev[l] == t0.src) ? 1 : 0;
   *radius = R;
   *axes = axes_code;
-  bool all_periodic = !F.any_face;
-  for (int k = 0; k < F.nterms; ++k) all_periodic = all_periodic && F.term[k].periodic;
-  *mode = (canonical && unit && simple_post) ? (all_periodic ? 0 : 1) : 2;
+  // "clean" box: no output in it is outside a term's [lo, hi) and no boundary
+  // face touches it, so the predicate-free instantiation is exact there
+  bool clean = true;
+  for (int k = 0; k < F.nterms; ++k) {
+    const DevTerm<T>& t = F.term[k];
+    if (!t.periodic && (F.box_lo[t.axis] < t.lo || F.box_hi[t.axis] > t.hi)) clean = false;
+  }
+  for (int a = 0; a < 3; ++a)
+    for (int l = 0; l < F.depth; ++l) {
+      if (F.face[l][a][0] && F.box_lo[a] <= F.rim_lo[a] && F.rim_lo[a] < F.box_hi[a]) clean = false;
+      if (F.face[l][a][1] && F.box_lo[a] <= F.rim_hi[a] && F.rim_hi[a] < F.box_hi[a]) clean = false;
+    }
+  *mode = (canonical && unit && simple_post) ? (clean ? 0 : 1) : 2;
   return true;
 }
 

@@ -175,6 +175,7 @@ class Engine:
         self.H = None if self.slab is not None else 0     # ghost depth, fixed at the first executed step
         self.exact_div = os.environ.get("FD_B200_FAST_SCALE", "0") != "1"
         self.fuse = os.environ.get("FD_B200_NO_FUSE", "0") != "1"
+        self.split_rim = os.environ.get("FD_B200_NO_SPLIT", "0") != "1"
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
         default_poll = 1 if points < (1 << 20) else 64
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
@@ -328,16 +329,62 @@ class Engine:
             for (dim, side), _ in ls.face_items():
                 d.face[l][dim + pad][side] = ls.face_ptr(dim, side, t + 1)
         d.flags = self.flags.data_ptr()
-        d.range_dim = -1
         for a in range(3):
             d.rim_lo[a], d.rim_hi[a] = 0, max(dims3[a] - 1, 0)
+        region = [[0, dims3[a]] for a in range(3)]
         if self.H:
             # only the owned planes are computed; the domain faces of the slab
             # axis sit on the first / last owned plane of the end ranks
-            d.range_dim, d.range_begin, d.range_end = pad, self.H, self.H + dot_state.owned0
+            region[pad] = [self.H, self.H + dot_state.owned0]
             d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
-        nat.check(self._fn["fd_fused_step"](C.byref(d), self.stream))
+        launch = self._fn["fd_fused_step"]
+        for box in self._split_boxes(d, region):
+            for a in range(3):
+                d.box_lo[a], d.box_hi[a] = box[a]
+            nat.check(launch(C.byref(d), self.stream))
         return True
+
+    def _split_boxes(self, d, region):
+        """Interior box first, then the rim slabs around it.
+
+        In the interior no output falls outside a fixed axis' [lo, hi) and no
+        boundary face applies, so the kernel runs its predicate-free
+        instantiation there; the thin rim slabs take the bounded one.  Every
+        point is still computed exactly once, in one pass."""
+        if not self.split_rim:
+            return [region]
+        inner = [list(r) for r in region]
+        for k in range(d.nterms):
+            tm = d.term[k]
+            if not tm.periodic:
+                inner[tm.axis][0] = max(inner[tm.axis][0], tm.lo)
+                inner[tm.axis][1] = min(inner[tm.axis][1], tm.hi)
+        for l in range(d.depth):
+            for a in range(3):
+                if d.face[l][a][0]:
+                    inner[a][0] = max(inner[a][0], d.rim_lo[a] + 1)
+                if d.face[l][a][1]:
+                    inner[a][1] = min(inner[a][1], d.rim_hi[a])
+        if inner == region:
+            return [region]
+        # the contiguous axis is processed in whole vector groups
+        align = 64 * (16 // self.dtype.itemsize)
+        if inner[2] != region[2]:
+            lo = -(-inner[2][0] // align) * align
+            hi = inner[2][1] // align * align
+            inner[2] = [lo, hi]
+        vol = lambda b: max(0, b[0][1] - b[0][0]) * max(0, b[1][1] - b[1][0]) * max(0, b[2][1] - b[2][0])
+        if vol(inner) * 2 < vol(region):
+            return [region]
+        boxes = [inner]
+        cur = [list(r) for r in region]
+        for a in range(3):                       # peel the rim off axis by axis
+            if inner[a][0] > cur[a][0]:
+                boxes.append([list(c) if i != a else [cur[a][0], inner[a][0]] for i, c in enumerate(cur)])
+            if inner[a][1] < cur[a][1]:
+                boxes.append([list(c) if i != a else [inner[a][1], cur[a][1]] for i, c in enumerate(cur)])
+            cur[a] = list(inner[a])
+        return boxes
 
     def _local_range(self, der, owned_out):
         """[lo, hi) of a der along the slab axis in extended local plane indices:

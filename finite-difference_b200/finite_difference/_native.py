@@ -63,7 +63,7 @@ class Fused(C.Structure):
                 ("face", ((C.c_void_p * 2) * 3) * 2),
                 ("nan_count", C.c_void_p * 2),
                 ("flags", C.c_void_p),
-                ("range_dim", C.c_int32), ("range_begin", C.c_int32), ("range_end", C.c_int32),
+                ("box_lo", C.c_int32 * 3), ("box_hi", C.c_int32 * 3),
                 ("rim_lo", C.c_int32 * 3), ("rim_hi", C.c_int32 * 3)]
 
 

@@ -185,7 +185,7 @@ typedef struct fd_post {
  * Multi-GPU: a slab carries ghost planes along its decomposed dimension; the
  * caller exchanges them (NCCL send/recv), describes that dimension as
  * non-periodic with [lo, hi) = the planes it owns and restricts execution
- * with range_dim / range_begin / range_end. */
+ * with box_lo / box_hi. */
 typedef struct fd_fused {
   int32_t n[3];
   int32_t nterms;
@@ -200,12 +200,12 @@ typedef struct fd_fused {
   const void* face[2][3][2];
   void* nan_count[2]; /* device int64*, incremented by NaNs left in out[l]   */
   void* flags;        /* device int64[FD_NUM_FLAGS]                          */
-  /* Sub-range execution (slab decomposition, boundary/interior split): only
-   * points with range_begin <= index[range_dim] < range_end are computed and
-   * stored; range_dim < 0 means the whole slice.  With ghost planes around a
-   * slab the domain faces do not sit at index 0 / n-1: rim_lo[d] / rim_hi[d]
+  /* Sub-box execution (slab decomposition, interior/rim split): only points
+   * with box_lo[d] <= index[d] < box_hi[d] for every d are computed and
+   * stored; an all-zero box means the whole slice.  With ghost planes around
+   * a slab the domain faces do not sit at index 0 / n-1: rim_lo[d] / rim_hi[d]
    * give the index along d where face[l][d][0] / face[l][d][1] apply. */
-  int32_t range_dim, range_begin, range_end;
+  int32_t box_lo[3], box_hi[3];
   int32_t rim_lo[3], rim_hi[3];
 } fd_fused_t;
 

@@ -164,10 +164,10 @@ class FakeLib:
                 total = -total
             elif po.op == 5:
                 total = total * _arr(po.coef, size).reshape(n)
-        region = [slice(None)] * 3
-        if d.range_dim >= 0:
-            region[d.range_dim] = slice(d.range_begin, d.range_end)
-        region = tuple(region)
+        if any(d.box_hi):
+            region = tuple(slice(d.box_lo[a], d.box_hi[a]) for a in range(3))
+        else:
+            region = (slice(None),) * 3
         if d.dot_out:
             _arr(d.dot_out, size).reshape(n)[region] = total[region]
         rate = total

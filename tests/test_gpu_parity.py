@@ -93,7 +93,8 @@ def _heat(fd, shape, n_t, periodic, k, dt, ic, points=(-1, 0, 1), history="all")
 
 @pytest.mark.parametrize("shape,periodic", [((67, 45, 130), True), ((33, 129, 70), False), ((1000, 37), False),
                                             ((513, 300), True), ((5000,), True), ((3, 3, 3), True),
-                                            ((2, 2), False)])
+                                            ((2, 2), False), ((40, 130, 520), False), ((700, 1024), False),
+                                            ((3000,), False)])
 def test_heat_against_oracle_odd_shapes(fd, shape, periodic):
     """Shapes that do not divide the thread-block tiles, both boundary kinds."""
     ic = np.random.default_rng(11).random(shape)

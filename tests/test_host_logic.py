@@ -22,3 +22,54 @@ def test_scenario_unfused_only(name, monkeypatch):
     monkeypatch.setenv("FD_B200_NO_FUSE", "1")
     with fake_native.installed():
         run_and_compare(name, fd)
+
+
+@pytest.mark.parametrize("shape", [(10, 400), (16, 30, 768)])
+def test_interior_rim_split_fake_native(shape):
+    """Fixed boundaries on a grid wide enough for the interior/rim split: the
+    statement is issued as one predicate-free interior box plus rim slabs, and
+    the result is still the oracle's, bit for bit."""
+    import contextlib
+    import io
+    import numpy as np
+    from oracle import fd_numpy as O
+    names = ["x", "y", "z"][:len(shape)]
+    ic = np.random.default_rng(21).random(shape)
+    with fake_native.installed() as fake:
+        axes = {"t": np.arange(4) * 1e-3}
+        for n, a in zip(shape, names):
+            axes[a] = np.arange(n) * 1.0
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model(axes, "t")
+            T = fd.Field(m, "T", n_time_ders=1)
+            d2 = fd.Stencil([-1, 0, 1], 2)
+            T.set_IC_values(ic)
+            for a in names:
+                T.set_BC("0", a, "start")
+                T.set_BC("1", a, "end")
+            while not m.finished:
+                acc = d2.der(T.prev, names[0])
+                for a in names[1:]:
+                    acc = acc + d2.der(T.prev, a)
+                T.dot.assign_update(0.1 * acc)
+                T.time_integrate_update()
+                m.increment_time()
+        got, got_dot = T.data, T.dot.data
+        assert fake.launches >= 3 * 4   # interior + rim slabs per step (the NaN count of the IC adds one)
+    # oracle with the same boundary values
+    g = O.Grid(axes, "t")
+    S, Sd = O.Series(g), O.Series(g)
+    S.data[0] = ic
+    for a in names:
+        S.set_face(a, "start", 0.0)
+        S.set_face(a, "end", 1.0)
+    st = O.StencilSpec([-1, 0, 1], 2)
+    while g.step + 1 < g.n_t:
+        acc = st.apply(g, S.data[g.step], names[0])
+        for a in names[1:]:
+            acc = acc + st.apply(g, S.data[g.step], a)
+        Sd.store(g.step + 1, 0.1 * acc)
+        O.integrate(S, Sd, g)
+        g.step += 1
+    assert np.array_equal(got, S.data, equal_nan=True)
+    assert np.array_equal(got_dot, Sd.data, equal_nan=True)
