@@ -62,6 +62,8 @@ class Device:
         # kernels run on torch's current stream so that torch.cuda.Event timing
         # and NCCL ordering see them; copies to the host run on a side stream
         self.copy_stream = t.cuda.Stream(device=self.dev)
+        # halo exchanges of a slab-decomposed model run here, ahead of the interior kernel
+        self.comm_stream = t.cuda.Stream(device=self.dev, priority=-1)
 
     # -- streams ---------------------------------------------------------
     @property

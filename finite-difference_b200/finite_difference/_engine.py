@@ -58,6 +58,8 @@ class FieldState:
         self.ring = [engine.dev.empty(self.ext_size, engine.dtype) for _ in range(depth)]
         self.held = [-1] * depth          # time index each slot holds
         self.halo_ok = [False] * depth    # ghost planes of the slot are current
+        self.halo_event = [None] * depth  # ... once this event (comm stream) has completed
+        self.wants_ghosts = False         # some statement differentiates this field along the slab axis
         self.saved = set()                # time indices already in the host history
         self.faces = None                 # {(dim, side): (tensor, per_time_elems or 0)}
         self.counts = engine.dev.zeros_i64(engine.n_t) if self.integrated else None
@@ -115,10 +117,17 @@ class FieldState:
     def refresh_ghosts(self, t):
         """Halo exchange for time level ``t`` (no-op when already current)."""
         k = 0 if self.constant else self.slot_index(t)
-        if self.H and not self.halo_ok[k]:
+        if not self.H:
+            return
+        self.wants_ghosts = True
+        if not self.halo_ok[k]:
             self.engine.slab.exchange(self.ring[k], self.plane, self.owned0, self.H)
             self.halo_ok[k] = True
             self.engine.stats["halo_exchanges"] = self.engine.stats.get("halo_exchanges", 0) + 1
+        elif self.halo_event[k] is not None:
+            # exchanged ahead of time on the comm stream: order the consumer after it
+            self.engine.dev.stream.wait_event(self.halo_event[k])
+            self.halo_event[k] = None
 
     # -- boundary faces ------------------------------------------------------
     def build_faces(self):
@@ -176,6 +185,7 @@ class Engine:
         self.exact_div = os.environ.get("FD_B200_FAST_SCALE", "0") != "1"
         self.fuse = os.environ.get("FD_B200_NO_FUSE", "0") != "1"
         self.split_rim = os.environ.get("FD_B200_NO_SPLIT", "0") != "1"
+        self.overlap = os.environ.get("FD_B200_NO_OVERLAP", "0") != "1"
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
         default_poll = 1 if points < (1 << 20) else 64
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
@@ -338,11 +348,51 @@ class Engine:
             region[pad] = [self.H, self.H + dot_state.owned0]
             d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
         launch = self._fn["fd_fused_step"]
-        for box in self._split_boxes(d, region):
-            for a in range(3):
-                d.box_lo[a], d.box_hi[a] = box[a]
-            nat.check(launch(C.byref(d), self.stream))
+
+        def run(piece):
+            for box in self._split_boxes(d, piece):
+                for a in range(3):
+                    d.box_lo[a], d.box_hi[a] = box[a]
+                nat.check(launch(C.byref(d), self.stream))
+
+        # (decided from facts every rank shares: slabs differ in size, collectives must not)
+        eager = [ls for ls in levels if ls.H and ls.wants_ghosts and min(self.slab.counts) >= 3 * ls.H]
+        if eager and self.overlap:
+            # boundary planes first, their exchange on the comm stream, then the
+            # interior while the planes travel over NVLink
+            lo, hi = region[pad]
+            for cut in ([lo, lo + self.H], [hi - self.H, hi]):
+                run([list(r) if a != pad else cut for a, r in enumerate(region)])
+            self._exchange_ahead(eager, t + 1)
+            run([list(r) if a != pad else [lo + self.H, hi - self.H] for a, r in enumerate(region)])
+        else:
+            run(region)
         return True
+
+    def _exchange_ahead(self, states, t):
+        """Halo exchange of freshly written boundary planes on the comm stream."""
+        dev = self.dev
+        if dev.comm_stream is None:          # CPU stand-in: same order of operations, synchronously
+            for st in states:
+                k = st.slot_index(t)
+                self.slab.exchange(st.ring[k], st.plane, st.owned0, st.H)
+                st.halo_ok[k], st.halo_event[k] = True, None
+                self.stats["halo_exchanges"] = self.stats.get("halo_exchanges", 0) + 1
+            return
+        import torch
+        ready = dev.event()
+        ready.record(dev.stream)
+        with torch.cuda.stream(dev.comm_stream):
+            dev.comm_stream.wait_event(ready)
+            for st in states:
+                k = st.slot_index(t)
+                self.slab.exchange(st.ring[k], st.plane, st.owned0, st.H)
+            done = dev.event()
+            done.record(dev.comm_stream)
+        for st in states:
+            k = st.slot_index(t)
+            st.halo_ok[k], st.halo_event[k] = True, done
+            self.stats["halo_exchanges"] = self.stats.get("halo_exchanges", 0) + 1
 
     def _split_boxes(self, d, region):
         """Interior box first, then the rim slabs around it.

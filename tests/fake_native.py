@@ -204,6 +204,7 @@ class FakeDevice:
     def __init__(self):
         self.dev = torch.device("cpu")
         self.copy_stream = None
+        self.comm_stream = None
 
     stream = None
     stream_ptr = 0

@@ -23,7 +23,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def launch(world, backend, names, extra_env=None, timeout=600):
+def launch(world, backend, names, extra_env=None, timeout=180):
     port = _free_port()
     procs = []
     for rank in range(world):
