@@ -193,6 +193,16 @@ def sample_shape(workload, target_points):
     return tuple(min(side, n) for n in full)
 
 
+
+def _nccl_options():
+    """NCCL kernels on a high-priority stream, so that a halo exchange issued
+    while the interior kernel still has blocks to dispatch is not queued behind it."""
+    import torch.distributed as dist
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.is_high_priority_stream = True
+    return opts
+
+
 # ------------------------------------------------------------------- arms
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -240,7 +250,7 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=_nccl_options())
     import finite_difference as fd
     from finite_difference import _device
 
@@ -279,17 +289,21 @@ def run_b200(args):
     torch.cuda.empty_cache()
 
     # ---- end to end through the public API with host buffers -------------
+    def end_to_end(steps):
+        t0 = time.perf_counter()
+        m2, F2, step2 = build_model(fd, args.workload, steps + 1, ic, world=world)
+        for _ in range(steps):
+            step2()
+        out = F2.local_level(steps)          # device -> pinned host, synchronous
+        m2.synchronize()
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0, out
+
+    end_to_end(W)                            # warm-up: allocator pools (device ring, pinned host level)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    t0 = time.perf_counter()
-    m2, F2, step2 = build_model(fd, args.workload, K + 1, ic, world=world)
-    for _ in range(K):
-        step2()
-    final = F2.local_level(K)
-    m2.synchronize()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
+    e2e_s, final = end_to_end(K)
     if world > 1:
         t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -7,9 +7,19 @@ import torch
 import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "finite-difference_b200")]
+
+
+def _nccl_options():
+    """NCCL kernels on a high-priority stream, so that a halo exchange issued
+    while the interior kernel still has blocks to dispatch is not queued behind it."""
+    import torch.distributed as dist
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.is_high_priority_stream = True
+    return opts
+
 local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
-dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=_nccl_options())
 import bench
 import finite_difference as fd
 from finite_difference import _dist

@@ -18,12 +18,22 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 
+
+def _nccl_options():
+    """NCCL kernels on a high-priority stream, so that a halo exchange issued
+    while the interior kernel still has blocks to dispatch is not queued behind it."""
+    import torch.distributed as dist
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.is_high_priority_stream = True
+    return opts
+
+
 def main():
     backend, names = sys.argv[1], sys.argv[2:]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     if backend == "nccl":
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)) % torch.cuda.device_count())
-        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()), pg_options=_nccl_options())
     else:
         dist.init_process_group("gloo")
     import finite_difference as fd
