@@ -45,7 +45,10 @@ WORKLOADS = {
     "c2": ("2-D heat diffusion 8192^2 fp64, 5-point stencil, fixed BCs (BASELINE.json configs[1])", (8192, 8192), 16),
     "c4": ("2-D wave equation 8192^2 fp64, n_time_ders=2, 9-point-per-axis stencils, periodic (BASELINE.json configs[3])",
            (8192, 8192), 32),
+    "c5": ("3-D staggered cell/edge acoustic model fp32, periodic, 256x2048x2048 slab per GPU "
+           "(2048^3 on 8 GPUs, BASELINE.json configs[4])", (256, 2048, 2048), 32),
 }
+DTYPES = {"c5": np.float32}
 K_DIFF, DT = 0.1, 1e-3
 
 
@@ -130,9 +133,28 @@ def build_model(fd, workload, n_t, ic, history="last", world=1):
     axes = {"t": np.arange(n_t) * DT}
     for n, a in zip(shape, names):
         axes[a] = np.arange(n) * 1.0
-    periodic = workload in ("c3", "c4")
+    periodic = workload in ("c3", "c4", "c5")
     with contextlib.redirect_stdout(io.StringIO()):
-        m = fd.Model(axes, "t", periodic=tuple(names) if periodic else (), history=history)
+        m = fd.Model(axes, "t", periodic=tuple(names) if periodic else (), history=history,
+                     dtype=DTYPES.get(workload, np.float64))
+        if workload == "c5":
+            p = fd.Field(m, "p", n_time_ders=1)
+            v = {a: fd.Field(m, "v" + a, edge_axes=(a,), n_time_ders=1) for a in names}
+            d_ce = fd.Stencil([-.5, .5], 1, "cell", "edge")
+            d_ec = fd.Stencil([-.5, .5], 1, "edge", "cell")
+            p.set_IC_values(ic)
+            for a in names:
+                v[a].set_IC("0")
+
+            def step():
+                for a in names:
+                    v[a].dot.assign_update((-1 / 1.0) * d_ce.der(p.prev, a))
+                    v[a].time_integrate_update()
+                div = d_ec.der(v["x"].new, "x") + d_ec.der(v["y"].new, "y") + d_ec.der(v["z"].new, "z")
+                p.dot.assign_update((-0.25) * div)
+                p.time_integrate_update()
+                m.increment_time()
+            return m, p, step
         if workload == "c4":
             u = fd.Field(m, "u", n_time_ders=2)
             st = fd.Stencil(list(range(-4, 5)), 2)
@@ -259,7 +281,9 @@ def run_b200(args):
     K, W = args.steps, args.warmup
 
     # ---- device-resident run --------------------------------------------
-    pinned = torch.empty(int(points), dtype=torch.float64, pin_memory=True)
+    np_dtype = DTYPES.get(args.workload, np.float64)
+    pinned = torch.empty(int(points), dtype=torch.float32 if np_dtype == np.float32 else torch.float64,
+                         pin_memory=True)
     ic = pinned.numpy().reshape(shape)
     ic[...] = np.random.default_rng(rank).random(shape)
     m, F, step = build_model(fd, args.workload, W + K + 2, ic, world=world)
@@ -309,7 +333,7 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     assert final.shape == tuple(shape) and np.isfinite(final[::7]).all()
-    bytes_level = points * 8
+    bytes_level = points * np.dtype(np_dtype).itemsize
 
     if rank != 0:
         if world > 1:
@@ -322,9 +346,9 @@ def run_b200(args):
     line = {
         "metric": "grid-point updates/sec", "value": value, "unit": "point-updates/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f32" if np_dtype == np.float32 else "f64", "data": "synthetic",
         "config": {"workload": desc, "grid_per_gpu": "x".join(map(str, shape)),
-                   "l2": "inputs larger than L2 (state level = %.0f MiB vs 126 MB L2)" % (points * 8 / 2 ** 20),
+                   "l2": "inputs larger than L2 (state level = %.0f MiB vs 126 MB L2)" % (bytes_level / 2 ** 20),
                    "multi_gpu": (f"slab decomposition along x over {world} ranks, NCCL send/recv halo exchange every step"
                                  if world > 1 else "single GPU"),
                    "history": "last", "engine_stats": stats},

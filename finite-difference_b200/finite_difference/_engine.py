@@ -77,11 +77,15 @@ class FieldState:
     def load_level(self, t):
         """Host history -> device (initial condition, constant coefficient)."""
         eng = self.engine
-        level = self.field._hist.direct_level(t)
-        if level is None:
-            level = self.field._hist.read({eng.model.time_axis: t})
         k = self.slot_index(t)
-        eng.dev.upload(level, eng.dtype, out=self.owned(self.ring[k]))
+        uniform = self.field._hist.uniform_level(t)
+        if uniform is not None:             # e.g. set_IC("0"): filled on the device
+            nat.check(eng._fn["fd_fill"](ptr(self.owned(self.ring[k])), uniform, self.size, eng.stream))
+        else:
+            level = self.field._hist.direct_level(t)
+            if level is None:
+                level = self.field._hist.read({eng.model.time_axis: t})
+            eng.dev.upload(level, eng.dtype, out=self.owned(self.ring[k]))
         self.held[k] = t
         self.halo_ok[k] = False
         self.saved.add(t)

@@ -129,6 +129,17 @@ class HostHistory:
             return hits[0].values
         return None
 
+    def uniform_level(self, t):
+        """The single value of time level ``t`` when one broadcast write (an
+        expression without axis names, e.g. set_IC("0")) is all it holds."""
+        if self.dense is not None or t in self.levels:
+            return None
+        hits = [e for e in self.log
+                if self.time_axis not in e.fixed or e.fixed[self.time_axis] == t]
+        if len(hits) == 1 and hits[0].fixed == {self.time_axis: t} and hits[0].values.size == 1:
+            return float(hits[0].values.reshape(()))
+        return None
+
     # -- write ---------------------------------------------------------------
     def write(self, location, values, copy=True):
         """Merge ``values`` (NaN = leave untouched) into the region."""

@@ -99,27 +99,27 @@ def der(f, points, weights, der_order, axis, periodic, from_edge, to_edge, dx):
     """
     shifts, shape_shift = stencil_shifts(points, from_edge, to_edge)
     if periodic:
-        out = np.zeros(f.shape)
+        out = np.zeros(f.shape, dtype=f.dtype)   # f.dtype: float64 in the reference; float32 restates the fp32 option
         for w, s in zip(weights, shifts):
             out += w * np.roll(f, -s, axis=axis)
     else:
         out_shape = list(f.shape)
         out_shape[axis] += shape_shift
-        out = np.full(tuple(out_shape), np.nan)
+        out = np.full(tuple(out_shape), np.nan, dtype=f.dtype)
         right_guard = 1 if (from_edge and not to_edge) else 0
         lo_shift = min(shifts[0], 0)
         hi_shift = max(shifts[-1], right_guard)
         span = f.shape[axis] + lo_shift - hi_shift
         part_shape = list(out_shape)
         part_shape[axis] = span
-        part = np.zeros(part_shape)
+        part = np.zeros(part_shape, dtype=f.dtype)
         sel = [slice(None)] * f.ndim
         for w, s in zip(weights, shifts):
             sel[axis] = slice(s - lo_shift, s - lo_shift + span)
             part += w * f[tuple(sel)]
         sel[axis] = slice(-lo_shift, -lo_shift + span)
         out[tuple(sel)] = part
-    out /= dx ** der_order
+    out /= f.dtype.type(dx ** der_order)
     if np.any(np.isinf(out)):
         raise Instability(INSTABILITY_MSG)
     return out
@@ -273,10 +273,11 @@ class Series:
     grid: Grid
     edge_axes: tuple = ()
     data: np.ndarray = _dc_field(default=None)
+    dtype: type = np.float64
 
     def __post_init__(self):
         if self.data is None:
-            self.data = np.full((self.grid.n_t,) + self.grid.shape(self.edge_axes), np.nan)
+            self.data = np.full((self.grid.n_t,) + self.grid.shape(self.edge_axes), np.nan, dtype=self.dtype)
 
     def set_face(self, axis, side, values):
         """Write a boundary face for all times (FD.py:361-385, 541-576 with
@@ -285,7 +286,7 @@ class Series:
         sel = [slice(None)] * self.data.ndim
         sel[k] = 0 if side == "start" else -1
         sel = tuple(sel)
-        new = np.array(np.broadcast_to(values, self.data[sel].shape), dtype=np.float64)
+        new = np.array(np.broadcast_to(values, self.data[sel].shape), dtype=self.data.dtype)
         merged, _ = merge(self.data[sel], new)
         self.data[sel] = merged
 
@@ -318,7 +319,7 @@ class StencilSpec:
 def integrate(series: Series, dot: Series, grid: Grid):
     """time_integrate_update (FD.py:500-538) incl. the two NaN counts."""
     t = grid.step
-    new = euler(series.data[t], dot.data[t + 1], grid.dt)
+    new = euler(series.data[t], dot.data[t + 1], series.data.dtype.type(grid.dt))
     series.store(t + 1, new)
     lost = int(np.isnan(series.data[t + 1]).sum()) > int(np.isnan(series.data[t]).sum())
     return lost and (t + 1) > 1
@@ -327,7 +328,7 @@ def integrate(series: Series, dot: Series, grid: Grid):
 # ---- the five BASELINE.json workloads -------------
 
 def run_heat(shape, n_t, periodic, k, dt, ic, bc_value=0.0, stencil_points=(-1, 0, 1),
-             dx=1.0, keep_dot=True):
+             dx=1.0, keep_dot=True, dtype=np.float64):
     """C.1-C.3: dT/dt = k * sum_a d2T/da2.  ``shape`` is the spatial shape;
     fixed axes get Dirichlet ``bc_value`` on both faces.  Returns (T, Tdot)."""
     names = ["x", "y", "z", "w"][:len(shape)]
@@ -335,7 +336,7 @@ def run_heat(shape, n_t, periodic, k, dt, ic, bc_value=0.0, stencil_points=(-1, 
     for n, a in zip(shape, names):
         axes[a] = np.arange(n) * dx
     g = Grid(axes, "t", tuple(a for a in names if periodic))
-    T, Td = Series(g), Series(g)
+    T, Td = Series(g, dtype=dtype), Series(g, dtype=dtype)
     T.data[0] = ic
     if not periodic:
         for a in names:
@@ -378,7 +379,7 @@ def run_wave(shape, n_t, c2, dt, ic_u, ic_v, stencil_points=tuple(range(-4, 5)),
     return U.data, Ud.data, Udd.data
 
 
-def run_acoustic(shape, n_t, rho, K, dt, ic_p, dx=1.0, periodic=True):
+def run_acoustic(shape, n_t, rho, K, dt, ic_p, dx=1.0, periodic=True, dtype=np.float64):
     """C.5: staggered pressure/velocity system.  p on cells, v_a on the edges
     of axis a.  Fixed variant: wall BC v_a = 0 on both end edges.
     Returns (p, [v_a...])."""
@@ -387,9 +388,9 @@ def run_acoustic(shape, n_t, rho, K, dt, ic_p, dx=1.0, periodic=True):
     for n, a in zip(shape, names):
         axes[a] = np.arange(n) * dx
     g = Grid(axes, "t", tuple(names) if periodic else ())
-    P, Pd = Series(g), Series(g)
-    V = [Series(g, (a,)) for a in names]
-    Vd = [Series(g, (a,)) for a in names]
+    P, Pd = Series(g, dtype=dtype), Series(g, dtype=dtype)
+    V = [Series(g, (a,), dtype=dtype) for a in names]
+    Vd = [Series(g, (a,), dtype=dtype) for a in names]
     P.data[0] = ic_p
     for v, a in zip(V, names):
         v.data[0] = 0.0

@@ -172,3 +172,71 @@ def test_general_fused_kernel_without_star_specialisation():
     env = dict(os.environ, FD_B200_NO_STAR="1")
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stdout + out.stderr
+
+
+# ---------------------------------------------------------------- fp32 option
+def _acoustic(fd, shape, n_t, periodic, ic, dtype):
+    names = ("x", "y", "z")
+    axes = {"t": np.arange(n_t) * 0.1}
+    for n, a in zip(shape, names):
+        axes[a] = np.arange(n) * 1.0
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model(axes, "t", periodic=names if periodic else (), dtype=dtype)
+        p = fd.Field(m, "p", n_time_ders=1)
+        v = {a: fd.Field(m, "v" + a, edge_axes=(a,), n_time_ders=1) for a in names}
+        d_ce = fd.Stencil([-.5, .5], 1, "cell", "edge")
+        d_ec = fd.Stencil([-.5, .5], 1, "edge", "cell")
+        p.set_IC_values(ic)
+        for a in names:
+            v[a].set_IC("0")
+            if not periodic:
+                v[a].set_BC("0", a, "start")
+                v[a].set_BC("0", a, "end")
+        while not m.finished:
+            for a in names:
+                v[a].dot.assign_update((-1 / 1.0) * d_ce.der(p.prev, a))
+                v[a].time_integrate_update()
+            div = d_ec.der(v["x"].new, "x") + d_ec.der(v["y"].new, "y") + d_ec.der(v["z"].new, "z")
+            p.dot.assign_update((-0.25) * div)
+            p.time_integrate_update()
+            m.increment_time()
+    return m, p, v
+
+
+@pytest.mark.parametrize("periodic", [True, False])
+def test_fp32_staggered_acoustic(fd, periodic):
+    """fp32 option (not in the reference): bit-identical to the float32 numpy
+    restatement, and within the stated bound of the fp64 oracle: relative L2
+    error <= 1e-5 and max-abs error <= 1e-4 * max|p|."""
+    shape, n_t = (36, 40, 64), 21
+    ic64 = np.random.default_rng(31).random(shape)
+    ic32 = ic64.astype(np.float32)
+    m, p, v = _acoustic(fd, shape, n_t, periodic, ic32, np.float32)
+    got = p.data
+    want32, _ = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic32, periodic=periodic, dtype=np.float32)
+    assert np.array_equal(got, want32.astype(np.float64), equal_nan=True)
+    want64, _ = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic32.astype(np.float64), periodic=periodic)
+    err = got[-1] - want64[-1]
+    assert np.linalg.norm(err) / np.linalg.norm(want64[-1]) <= 1e-5
+    assert np.abs(err).max() <= 1e-4 * np.abs(want64[-1]).max()
+    assert m._engine.stats["unfused_statements"] == 0
+
+
+def test_fp32_heat_star_kernel(fd):
+    shape = (24, 40, 512)
+    ic32 = np.random.default_rng(32).random(shape).astype(np.float32)
+    names = ("x", "y", "z")
+    axes = {"t": np.arange(6) * 1e-3}
+    for n, a in zip(shape, names):
+        axes[a] = np.arange(n) * 1.0
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model(axes, "t", periodic=names, dtype=np.float32)
+        T = fd.Field(m, "T", n_time_ders=1)
+        d2 = fd.Stencil([-1, 0, 1], 2)
+        T.set_IC_values(ic32)
+        while not m.finished:
+            T.dot.assign_update(0.1 * (d2.der(T.prev, "x") + d2.der(T.prev, "y") + d2.der(T.prev, "z")))
+            T.time_integrate_update()
+            m.increment_time()
+    want, _ = O.run_heat(shape, 6, True, 0.1, 1e-3, ic32, dtype=np.float32)
+    assert np.array_equal(T.data, want.astype(np.float64), equal_nan=True)
