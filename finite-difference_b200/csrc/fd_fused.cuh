@@ -7,6 +7,56 @@
 
 namespace fdb {
 
+// ---- 128-bit vector access along the contiguous axis --------------------------
+template <typename T>
+struct Vec;
+template <>
+struct Vec<double> {
+  using type = double2;
+  static constexpr int N = 2;
+};
+template <>
+struct Vec<float> {
+  using type = float4;
+  static constexpr int N = 4;
+};
+
+template <typename T, int N>
+struct Pack {
+  T v[N];
+};
+
+template <typename T>
+__device__ __forceinline__ Pack<T, Vec<T>::N> load_vec(const T* p) {
+  using V = typename Vec<T>::type;
+  union {
+    V vec;
+    Pack<T, Vec<T>::N> pk;
+  } u;
+  u.vec = __ldg(reinterpret_cast<const V*>(p));
+  return u.pk;
+}
+
+template <typename T>
+__device__ __forceinline__ void store_vec(T* p, const Pack<T, Vec<T>::N>& pk) {
+  using V = typename Vec<T>::type;
+  union {
+    V vec;
+    Pack<T, Vec<T>::N> pk;
+  } u;
+  u.pk = pk;
+  *reinterpret_cast<V*>(p) = u.vec;
+}
+
+__device__ __forceinline__ int wrap_or_clamp(int i, int n, bool periodic) {
+  if (periodic) {
+    i += (i < 0) ? n : 0;
+    i -= (i >= n) ? n : 0;
+    return i;
+  }
+  return max(0, min(i, n - 1));
+}
+
 template <typename T>
 struct DevTerm {
   const T* src;

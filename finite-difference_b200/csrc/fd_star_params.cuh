@@ -23,19 +23,6 @@
 
 namespace fdb {
 
-template <typename T>
-struct Vec;
-template <>
-struct Vec<double> {
-  using type = double2;
-  static constexpr int N = 2;
-};
-template <>
-struct Vec<float> {
-  using type = float4;
-  static constexpr int N = 4;
-};
-
 constexpr int kMaxR = 4;
 
 template <typename T>
