@@ -15,11 +15,14 @@ int fail(const char* fmt, ...) { fprintf(stderr, "fail: %s\n", fmt); return 1; }
 }
 using namespace fdb;
 
+static int g_carveout = -1;
+
 template <int OCC, int VPT>
 static float run(StarParams<double> P, double* a, double* b, int bx, int by, int chunk, int iters) {
   const int n0 = P.F.n[0], n1 = P.F.n[1], nvec = P.F.n[2] / 2 / VPT;
   dim3 grid((P.F.n[2] / 2 + bx * VPT - 1) / (bx * VPT), (n1 + by - 1) / by, (n0 + chunk - 1) / chunk), block(bx, by, 1);
   P.x_chunk = chunk;
+  cudaFuncSetAttribute(star_kernel<double, 1, 3, 0, VPT, OCC>, cudaFuncAttributePreferredSharedMemoryCarveout, g_carveout);
   cudaEvent_t e0, e1;
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
@@ -72,17 +75,10 @@ int main() {
   if (!star_applicable<double>(F, &P, &R, &axes, &mode)) { printf("not applicable\n"); return 1; }
   printf("R=%d axes=%d mode=%d\n", R, axes, mode);
   const int iters = 30;
-  const int shapes[][2] = {{32, 8}, {32, 4}, {32, 6}};
-  const int chunks[] = {4, 6, 8, 12, 16};
-  for (auto& s : shapes)
-    for (int c : chunks) {
-      if (s[0] * s[1] > 256 && false) continue;
-      float m1 = run<4, 1>(P, a, b, s[0], s[1], c, iters);
-      float m2 = run<2, 2>(P, a, b, s[0], s[1], c, iters);
-      float m3 = run<3, 2>(P, a, b, s[0], s[1], c, iters);
-      float m4 = run<4, 2>(P, a, b, s[0], s[1], c, iters);
-      printf("block %2dx%-2d chunk %3d : vpt1/occ4 %.4f  vpt2/occ2 %.4f  vpt2/occ3 %.4f  vpt2/occ4 %.4f ms  (%.0f GB/s best)\n",
-             s[0], s[1], c, m1, m2, m3, m4, N * 16.0 / (fmin(fmin(m1, m2), fmin(m3, m4)) * 1e-3) / 1e9);
-    }
+  for (int cv : {-1, 0, 25, 50, 100}) {
+    g_carveout = cv;
+    printf("carveout %3d: vpt2/occ3 32x8 chunk8 %.4f ms   chunk16 %.4f ms\n", cv, run<3, 2>(P, a, b, 32, 8, 8, 30),
+           run<3, 2>(P, a, b, 32, 8, 16, 30));
+  }
   return 0;
 }
