@@ -190,6 +190,7 @@ class Engine:
         self.fuse = os.environ.get("FD_B200_NO_FUSE", "0") != "1"
         self.split_rim = os.environ.get("FD_B200_NO_SPLIT", "0") != "1"
         self.overlap = os.environ.get("FD_B200_NO_OVERLAP", "0") != "1"
+        self.fuse_pairs = os.environ.get("FD_B200_NO_PAIR", "0") != "1"
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
         default_poll = 1 if points < (1 << 20) else 64
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
@@ -198,7 +199,7 @@ class Engine:
         self.stats = {"fused": 0, "unfused_statements": 0}
         self._fn = {name: nat.fn(name, self.dtype) for name in
                     ("fd_der", "fd_ewise", "fd_merge_store", "fd_fill", "fd_face_store", "fd_count_nan",
-                     "fd_fused_step")}
+                     "fd_fused_step", "fd_fused_pair")}
 
     # ------------------------------------------------------------------ utils
     def state(self, field):
@@ -237,6 +238,9 @@ class Engine:
                 _collect_new_reads(node, t + 1, reads_new)
         memo = {}
         consumed = set()
+        if self.fuse and self.fuse_pairs and self._try_pair(stmts, t, reads_new):
+            consumed = set(range(len(stmts)))
+            self.stats["fused_pairs"] = self.stats.get("fused_pairs", 0) + 1
         for i, (kind, field, node) in enumerate(stmts):
             if i in consumed:
                 continue
@@ -452,6 +456,131 @@ class Engine:
         lo = max(lo_g, first) - first + self.H
         hi = min(hi_g, first + owned_out) - first + self.H
         return lo, max(hi, lo)
+
+
+    # ------------------------------------------------- fused staggered pair
+    def _try_pair(self, stmts, t, reads_new):
+        """The whole step is  v_a += dt*c_a*up.der(p.prev, a)  for some axes a, then
+        p += dt*c*(sum_a down.der(v_a.new, a))  (cell/edge leapfrog):
+        one launch of fd_fused_pair instead of len(axes)+1 fused statements."""
+        n = len(stmts)
+        if n < 4 or n % 2 or n > 8:
+            return False
+        kinds = [k for k, _, _ in stmts]
+        if kinds != ["assign", "integrate"] * (n // 2):
+            return False
+        for i in range(0, n, 2):                       # assign(F.dot) directly followed by integrate(F)
+            if stmts[i][1]._parent is not stmts[i + 1][1] or stmts[i + 1][1]._parent is not None:
+                return False
+        p_field = stmts[n - 1][1]
+        p_state = self.state(p_field)
+        dims3 = p_state.dims3
+        vn = 16 // self.dtype.itemsize
+        if dims3 is None or dims3[2] % vn or dims3[2] < 3 * vn:
+            return False
+        shape = tuple(p_field._slice_shape)
+        pad = 3 - len(shape)
+        down = _match_statement(stmts[n - 2][2])
+        if down is None:
+            return False
+        terms, posts = down
+        if len(terms) != n // 2 - 1 or posts not in ([], [(nat.POST_MUL, posts[0][1] if posts else 0.0, None)]):
+            return False
+        ups = {}
+        for i in range(0, n - 2, 2):                   # the velocity statements
+            m = _match_statement(stmts[i][2])
+            if m is None:
+                return False
+            (uterms, uposts), vfield = m, stmts[i + 1][1]
+            if len(uterms) != 1 or uposts not in ([], [(nat.POST_MUL, uposts[0][1] if uposts else 0.0, None)]):
+                return False
+            der, _, pre, negate = uterms[0]
+            if (negate or (pre is not None and uposts) or der.shifts != (-1, 0) or not isinstance(der.a, Leaf)
+                    or der.a.field is not p_field or der.a.t != t or tuple(vfield._slice_shape) != shape):
+                return False
+            # `c * der` is matched as a pre-scaled term; as a post-multiplication it rounds the same
+            c_up = pre if pre is not None else (uposts[0][1] if uposts else 1.0)
+            ups[id(vfield)] = (vfield, der, c_up)
+        fields = [p_field, p_field.dot] + [f for f, _, _ in ups.values()] + [f.dot for f, _, _ in ups.values()]
+        if any(f._bc_locations for f in fields) or len(ups) != len(terms):
+            return False
+        d = nat.Pair()
+        used = set()
+        for k, (der, subtract, pre, negate) in enumerate(terms):
+            leaf = der.a
+            got = ups.get(id(leaf.field)) if isinstance(leaf, Leaf) else None
+            if (got is None or leaf.t != t + 1 or pre is not None or negate or der.shifts != (0, 1)
+                    or got[1].axis != der.axis or der.axis in used):
+                return False
+            used.add(der.axis)
+            vfield, uder, c_up = got
+            slab_axis = self.H and der.axis == 0
+            if not (der.periodic or slab_axis) or not (uder.periodic or slab_axis):
+                return False
+            if slab_axis and self.H != 1:
+                return False
+            ax = d.ax[k]
+            ax.axis, ax.periodic, ax.subtract = der.axis + pad, 0 if slab_axis else 1, 1 if subtract else 0
+            ax.c_up = c_up
+            ax.up = nat.make_stencil(uder.shifts, uder.weights, uder.scale, self.exact_div)
+            ax.down = nat.make_stencil(der.shifts, der.weights, der.scale, self.exact_div)
+        # every axis of the grid that is not differentiated must not matter; every
+        # differentiated one is periodic or the slab axis: nothing can be NaN-masked
+        if self.H and 0 not in used:
+            return False
+
+        # ---- all checks passed: claim levels and launch
+        for a in range(3):
+            d.n[a] = dims3[a]
+        d.naxes = len(terms)
+        if self.H:
+            p_state.refresh_ghosts(t)
+        d.p_prev = p_state.level(t).data_ptr()
+        d.c_down = posts[0][1] if posts else 1.0
+        d.dt = float(self.model.dt)
+        outs = []
+        for k, (der, _, _, _) in enumerate(terms):
+            vfield = der.a.field
+            vs, vds = self.state(vfield), self.state(vfield.dot)
+            if self.H and der.axis == 0:
+                vs.refresh_ghosts(t)
+            ax = d.ax[k]
+            ax.v_prev = vs.level(t).data_ptr()
+            ax.v_out = vs.claim(t + 1).data_ptr()
+            ax.v_nan_count = vs.counts.data_ptr() + 8 * (t + 1)
+            want = id(vfield.dot) in reads_new or self.wants_level(t + 1)
+            ax.vdot_out = vds.claim(t + 1).data_ptr() if want else 0
+            if not want:
+                vds.held[0] = -1
+            outs.append(vs)
+        pd_state = self.state(p_field.dot)
+        d.p_out = p_state.claim(t + 1).data_ptr()
+        d.p_nan_count = p_state.counts.data_ptr() + 8 * (t + 1)
+        want = id(p_field.dot) in reads_new or self.wants_level(t + 1)
+        d.pdot_out = pd_state.claim(t + 1).data_ptr() if want else 0
+        if not want:
+            pd_state.held[0] = -1
+        d.flags = self.flags.data_ptr()
+        region = [[0, dims3[a]] for a in range(3)]
+        if self.H:
+            region[pad] = [self.H, self.H + p_state.owned0]
+        launch = self._fn["fd_fused_pair"]
+
+        def run(piece):
+            for a in range(3):
+                d.box_lo[a], d.box_hi[a] = piece[a]
+            nat.check(launch(C.byref(d), self.stream))
+
+        eager = [st for st in [p_state] + outs if st.H and st.wants_ghosts and min(self.slab.counts) >= 3 * st.H]
+        if eager and self.overlap:
+            lo, hi = region[pad]
+            for cut in ([lo, lo + self.H], [hi - self.H, hi]):
+                run([list(r) if a != pad else cut for a, r in enumerate(region)])
+            self._exchange_ahead(eager, t + 1)
+            run([list(r) if a != pad else [lo + self.H, hi - self.H] for a, r in enumerate(region)])
+        else:
+            run(region)
+        return True
 
     # --------------------------------------------------------- unfused path
     def _eval(self, node, memo):

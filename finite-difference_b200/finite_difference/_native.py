@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 FD_MAX_POINTS = 16
 FD_MAX_TERMS = 4
 FD_MAX_POST = 4
@@ -67,6 +67,22 @@ class Fused(C.Structure):
                 ("rim_lo", C.c_int32 * 3), ("rim_hi", C.c_int32 * 3)]
 
 
+class PairAxis(C.Structure):
+    _fields_ = [("v_prev", C.c_void_p), ("v_out", C.c_void_p), ("vdot_out", C.c_void_p),
+                ("v_nan_count", C.c_void_p), ("c_up", C.c_double),
+                ("axis", C.c_int32), ("periodic", C.c_int32), ("subtract", C.c_int32), ("_pad", C.c_int32),
+                ("up", Stencil), ("down", Stencil)]
+
+
+class Pair(C.Structure):
+    _fields_ = [("n", C.c_int32 * 3), ("naxes", C.c_int32),
+                ("ax", PairAxis * 3),
+                ("p_prev", C.c_void_p), ("p_out", C.c_void_p), ("pdot_out", C.c_void_p),
+                ("p_nan_count", C.c_void_p), ("flags", C.c_void_p),
+                ("c_down", C.c_double), ("dt", C.c_double),
+                ("box_lo", C.c_int32 * 3), ("box_hi", C.c_int32 * 3)]
+
+
 _I64, _P, _D, _I = C.c_int64, C.c_void_p, C.c_double, C.c_int
 
 # name -> (restype, argtypes); every symbol include/fd_b200.h declares
@@ -84,6 +100,7 @@ for _sfx in ("f64", "f32"):
         f"fd_face_store_{_sfx}": (_I, [_P, _P, _I64, _I64, _I64, _I64, _P]),
         f"fd_count_nan_{_sfx}": (_I, [_P, _I64, _P, _P]),
         f"fd_fused_step_{_sfx}": (_I, [C.POINTER(Fused), _P]),
+        f"fd_fused_pair_{_sfx}": (_I, [C.POINTER(Pair), _P]),
     })
 
 

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define FD_ABI_VERSION 2
+#define FD_ABI_VERSION 3
 
 #define FD_MAX_POINTS 16 /* sample points per stencil                     */
 #define FD_MAX_TERMS 4   /* der() terms summed by one fused statement     */
@@ -211,6 +211,48 @@ typedef struct fd_fused {
 
 int fd_fused_step_f64(const fd_fused_t* desc, void* stream);
 int fd_fused_step_f32(const fd_fused_t* desc, void* stream);
+
+/* ---- fused staggered pair: the velocity updates and the pressure update of a
+ *      cell/edge leapfrog step in ONE pass ---------------------------------- */
+
+/* For every listed axis a (user script):
+ *     v_a.dot.assign_update(c_up * up.der(p.prev, a));  v_a.time_integrate_update()
+ * and then
+ *     p.dot.assign_update(c_down * (sum_a down.der(v_a.new, a)));  p.time_integrate_update()
+ * i.e. 2*(naxes+1) statements of FD.py:478-538 with the der calls of
+ * FD.py:990-1122 between them.  The kernel recomputes v_a.new at the second
+ * sample point instead of reading it back, so each field is read once and
+ * written once.  `up` is a cell->edge stencil with shifts (-1, 0), `down` an
+ * edge->cell stencil with shifts (0, +1); every axis must be periodic or be the
+ * decomposed axis of a slab (ghost planes, box_lo/box_hi = owned planes). */
+typedef struct fd_pair_axis {
+  const void* v_prev;
+  void* v_out;
+  void* vdot_out;     /* optional: v_a.dot at t+1 */
+  void* v_nan_count;  /* device int64*, may be NULL */
+  double c_up;
+  int32_t axis;       /* 0,1,2 in the collapsed view */
+  int32_t periodic;   /* 0: the axis carries ghost planes (slab) */
+  int32_t subtract;   /* 1: this term is subtracted in the sum (first term: ignored) */
+  int32_t _pad;
+  fd_stencil_t up, down;
+} fd_pair_axis_t;
+
+typedef struct fd_pair {
+  int32_t n[3];
+  int32_t naxes;
+  fd_pair_axis_t ax[3];
+  const void* p_prev;
+  void* p_out;
+  void* pdot_out;     /* optional */
+  void* p_nan_count;
+  void* flags;
+  double c_down, dt;
+  int32_t box_lo[3], box_hi[3];
+} fd_pair_t;
+
+int fd_fused_pair_f64(const fd_pair_t* desc, void* stream);
+int fd_fused_pair_f32(const fd_pair_t* desc, void* stream);
 
 #ifdef __cplusplus
 }

@@ -252,6 +252,36 @@ def acoustic3d_fixed(fd):
     return acoustic3d(fd, shape=(5, 6, 4), periodic=False, seed=9)
 
 
+def acoustic3d_wide(fd):
+    """Periodic staggered step on a grid wide enough for 128-bit vectors along z
+    (the B200 build runs it as ONE fused velocity+pressure launch per step)."""
+    return acoustic3d(fd, shape=(8, 5, 12), n_t=5, seed=14)
+
+
+def acoustic2d(fd, shape=(9, 16), n_t=5, seed=15):
+    """2-D staggered pair with unequal spacings and a subtraction in the divergence."""
+    names = ("x", "y")
+    m = fd.Model({"t": np.arange(n_t) * 0.05, "x": np.arange(shape[0]) * 0.5, "y": np.arange(shape[1]) * 2.0},
+                 "t", periodic=names)
+    p = fd.Field(m, "p", n_time_ders=1)
+    v = {a: fd.Field(m, "v" + a, edge_axes=(a,), n_time_ders=1) for a in names}
+    d_ce = fd.Stencil([-.5, .5], 1, "cell", "edge")
+    d_ec = fd.Stencil([-.5, .5], 1, "edge", "cell")
+    _inject_ic(p, 0, _rng(seed).random(shape))
+    for a in names:
+        _inject_ic(v[a], 0, _rng(seed + 1).random(shape) * 0.1)
+
+    def body():
+        for a in names:
+            v[a].dot.assign_update(d_ce.der(p.prev, a) * -0.7)
+            v[a].time_integrate_update()
+        p.dot.assign_update(0.3 * (d_ec.der(v["x"].new, "x") - d_ec.der(v["y"].new, "y")))
+        p.time_integrate_update()
+
+    _loop(m, body)
+    return {"p": p.data, "vx": v["x"].data, "vy": v["y"].data, "pdot": p.dot.data, "vxdot": v["x"].dot.data}
+
+
 # -- C.6 and general-DAG cases -------------------------------------------------
 
 def flux_1d(fd, n=11, n_t=6, seed=10):
@@ -363,6 +393,8 @@ ALL = {
     "wave2d_fixed_nan_spread": wave2d_fixed_nan_spread,
     "acoustic3d": acoustic3d,
     "acoustic3d_fixed": acoustic3d_fixed,
+    "acoustic3d_wide": acoustic3d_wide,
+    "acoustic2d": acoustic2d,
     "flux_1d": flux_1d,
     "variable_coefficient": variable_coefficient,
     "burgers_1d": burgers_1d,

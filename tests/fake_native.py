@@ -40,7 +40,7 @@ class FakeLib:
         self.error = b""
 
     def fd_abi_version(self):
-        return 2
+        return 3
 
     def fd_last_error(self):
         return self.error
@@ -196,6 +196,45 @@ class FakeLib:
                 _arr(d.nan_count[l], 1, np.int64)[0] += int(np.isnan(new[region]).sum())
             rate = new
         return 0
+
+
+def _pair(self, desc, stream):
+    """fd_fused_pair_f64 in numpy (periodic rolls; the box keeps clear of wrapped ghosts)."""
+    self.launches += 1
+    d = desc._obj if hasattr(desc, "_obj") else desc.contents
+    n = tuple(d.n)
+    size = int(np.prod(n))
+    region = tuple(slice(d.box_lo[a], d.box_hi[a]) for a in range(3)) if any(d.box_hi) else (slice(None),) * 3
+    flags = _arr(d.flags, 4, np.int64) if d.flags else None
+    p = _arr(d.p_prev, size).reshape(n)
+    total = None
+    for k in range(d.naxes):
+        A = d.ax[k]
+        u, w = list(A.up.weights[:2]), list(A.down.weights[:2])
+        v = _arr(A.v_prev, size).reshape(n)
+        g = ((0.0 + u[0] * np.roll(p, 1, axis=A.axis)) + u[1] * p) / A.up.scale
+        rhs = g * A.c_up
+        vnew = v + rhs * d.dt
+        dd = ((0.0 + w[0] * vnew) + w[1] * np.roll(vnew, -1, axis=A.axis)) / A.down.scale
+        if flags is not None and (np.any(np.isinf(g[region])) or np.any(np.isinf(dd[region]))):
+            flags[0] = 1
+        total = dd if k == 0 else (total - dd if A.subtract else total + dd)
+        _arr(A.v_out, size).reshape(n)[region] = vnew[region]
+        if A.vdot_out:
+            _arr(A.vdot_out, size).reshape(n)[region] = rhs[region]
+        if A.v_nan_count:
+            _arr(A.v_nan_count, 1, np.int64)[0] += int(np.isnan(vnew[region]).sum())
+    rhs = total * d.c_down
+    pnew = p + rhs * d.dt
+    _arr(d.p_out, size).reshape(n)[region] = pnew[region]
+    if d.pdot_out:
+        _arr(d.pdot_out, size).reshape(n)[region] = rhs[region]
+    if d.p_nan_count:
+        _arr(d.p_nan_count, 1, np.int64)[0] += int(np.isnan(pnew[region]).sum())
+    return 0
+
+
+FakeLib.fd_fused_pair_f64 = _pair
 
 
 class FakeDevice:

@@ -14,7 +14,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 SCENARIOS = ["heat3d_periodic", "heat3d_fixed", "heat2d_fixed", "heat2d_time_middle", "wave2d", "wave2d_5pt",
              "wave2d_fixed_nan_spread", "acoustic3d", "acoustic3d_fixed", "flux_1d", "variable_coefficient",
-             "burgers_1d", "readme_1d", "heat4d_periodic", "heat1d_odd_dx"]
+             "burgers_1d", "readme_1d", "acoustic3d_wide", "acoustic2d", "heat4d_periodic", "heat1d_odd_dx"]
 
 
 def _free_port():

@@ -220,6 +220,19 @@ def test_fp32_staggered_acoustic(fd, periodic):
     assert np.linalg.norm(err) / np.linalg.norm(want64[-1]) <= 1e-5
     assert np.abs(err).max() <= 1e-4 * np.abs(want64[-1]).max()
     assert m._engine.stats["unfused_statements"] == 0
+    if periodic:   # the whole step is one fused velocity+pressure launch
+        assert m._engine.stats.get("fused_pairs") == n_t - 1 and m._engine.stats["fused"] == 0
+
+
+def test_fp64_staggered_pair_kernel(fd):
+    shape, n_t = (20, 24, 130), 9
+    ic = np.random.default_rng(33).random(shape)
+    m, p, v = _acoustic(fd, shape, n_t, True, ic, np.float64)
+    want, want_v = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic)
+    assert np.array_equal(p.data, want, equal_nan=True)
+    for a, w in zip("xyz", want_v):
+        assert np.array_equal(v[a].data, w, equal_nan=True)
+    assert m._engine.stats.get("fused_pairs") == n_t - 1
 
 
 def test_fp32_heat_star_kernel(fd):

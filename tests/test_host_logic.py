@@ -17,6 +17,28 @@ def test_scenario_fake_native(name):
         assert fake.launches > 0
 
 
+def test_staggered_pair_is_one_launch_per_step():
+    import finite_difference.model as M
+    engines = []
+    orig = M.Model._get_engine
+
+    def spy(self):
+        e = orig(self)
+        if e not in engines:
+            engines.append(e)
+        return e
+
+    M.Model._get_engine = spy
+    try:
+        with fake_native.installed():
+            run_and_compare("acoustic3d_wide", fd)
+            assert engines[-1].stats.get("fused_pairs") == 4 and engines[-1].stats["fused"] == 0
+            run_and_compare("acoustic2d", fd)
+            assert engines[-1].stats.get("fused_pairs") == 4
+    finally:
+        M.Model._get_engine = orig
+
+
 @pytest.mark.parametrize("name", ["heat2d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d"])
 def test_scenario_unfused_only(name, monkeypatch):
     monkeypatch.setenv("FD_B200_NO_FUSE", "1")
