@@ -46,8 +46,17 @@ struct PairParams {
   T c_down, dt;
 };
 
-template <typename T, int NA>
-__global__ void __launch_bounds__(256, 2)
+// SCALE 0: every stencil divides by 1 (skipped); 1: by powers of two (exact
+// multiplication by the inverse); 2: general (IEEE division where needed).
+template <typename T, int SCALE>
+__device__ __forceinline__ T pair_scale(T v, int mode, T scale, T inv) {
+  if (SCALE == 0) return v;
+  if (SCALE == 1) return mul_rn(v, inv);
+  return apply_scale(v, mode, scale, inv);
+}
+
+template <typename T, int NA, int SCALE>
+__global__ void __launch_bounds__(256, sizeof(T) == 4 ? 3 : 2)
 pair_kernel(const __grid_constant__ PairParams<T> P) {
   constexpr int VN = Vec<T>::N;
   using PK = Pack<T, VN>;
@@ -118,16 +127,16 @@ pair_kernel(const __grid_constant__ PairParams<T> P) {
         for (int e = 0; e < VN; ++e) {
           // v update at this point ...
           T g = add_rn(add_rn((T)0, mul_rn(A.u0, pm[e])), mul_rn(A.u1, p0.v[e]));
-          g = apply_scale(g, A.u_mode, A.us, A.ui);
+          g = pair_scale<T, SCALE>(g, A.u_mode, A.us, A.ui);
           saw_inf |= is_inf(g);
           const T rhs0 = mul_rn(g, A.c_up);
           const T v0 = add_rn(vc[e], mul_rn(rhs0, P.dt));
           // ... and at the next point along the axis (recomputed, not re-read)
           T h = add_rn(add_rn((T)0, mul_rn(A.u0, p0.v[e])), mul_rn(A.u1, pp[e]));
-          h = apply_scale(h, A.u_mode, A.us, A.ui);
+          h = pair_scale<T, SCALE>(h, A.u_mode, A.us, A.ui);
           const T v1 = add_rn(vp[e], mul_rn(mul_rn(h, A.c_up), P.dt));
           T d = add_rn(add_rn((T)0, mul_rn(A.w0, v0)), mul_rn(A.w1, v1));
-          d = apply_scale(d, A.d_mode, A.ds, A.di);
+          d = pair_scale<T, SCALE>(d, A.d_mode, A.ds, A.di);
           saw_inf |= is_inf(d);
           total[e] = (a == 0) ? d : (A.subtract ? sub_rn(total[e], d) : add_rn(total[e], d));
           nan_v[a] += is_nan(v0) ? 1u : 0u;
@@ -227,11 +236,26 @@ static int pair_impl(const fd_pair_t* d, void* stream) {
   while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.x_chunk = chunk;
   dim3 grid((nv + bx - 1) / bx, (unsigned)gy, (nx + chunk - 1) / chunk), block(bx, by, 1);
-  switch (d->naxes) {
-    case 1: pair_kernel<T, 1><<<grid, block, 0, (cudaStream_t)stream>>>(P); break;
-    case 2: pair_kernel<T, 2><<<grid, block, 0, (cudaStream_t)stream>>>(P); break;
-    default: pair_kernel<T, 3><<<grid, block, 0, (cudaStream_t)stream>>>(P); break;
+  int scale_class = 0;
+  for (int a = 0; a < d->naxes; ++a) {
+    const int m = P.ax[a].u_mode > P.ax[a].d_mode ? P.ax[a].u_mode : P.ax[a].d_mode;
+    if (m > scale_class) scale_class = m;
+    // mode 0 under class 1: multiplying by inv == 1 is exact
   }
+  cudaStream_t st = (cudaStream_t)stream;
+#define FD_PAIR(NA)                                                        \
+  if (scale_class == 0)                                                    \
+    pair_kernel<T, NA, 0><<<grid, block, 0, st>>>(P);                      \
+  else if (scale_class == 1)                                               \
+    pair_kernel<T, NA, 1><<<grid, block, 0, st>>>(P);                      \
+  else                                                                     \
+    pair_kernel<T, NA, 2><<<grid, block, 0, st>>>(P);
+  switch (d->naxes) {
+    case 1: FD_PAIR(1) break;
+    case 2: FD_PAIR(2) break;
+    default: FD_PAIR(3) break;
+  }
+#undef FD_PAIR
   return check_launch("fd_fused_pair");
 }
 
