@@ -285,6 +285,15 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
   if (F.depth > 1) warp_add_count(F.nan_count[1], nan_cnt[1]);
 }
 
+// FD_B200_NO_LEAN=1 keeps the general star kernel for every statement (tests).
+inline bool lean_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("FD_B200_NO_LEAN");
+    return !(e && e[0] == '1');
+  }();
+  return on;
+}
+
 // FD_B200_STAR_CHUNK=<planes> overrides the marching length (tuning runs only).
 inline int tuning_chunk() {
   static const int v = [] {
@@ -334,8 +343,15 @@ static void launch_star(StarParams<T>& P, cudaStream_t stream) {
   launch_star_vpt<T, R, AXES, MODE, 1>(P, bx, by, stream);
 }
 
+}  // namespace fdb
+
+#include "fd_star_lean.cuh"
+
+namespace fdb {
+
 template <typename T, int R>
 void dispatch_axes(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
+  if (lean_enabled() && try_star_lean<T, R>(P, axes, mode, stream)) return;
 #define FD_STAR(AX)                                    \
   if (mode == 0)                                       \
     launch_star<T, R, AX, 0>(P, stream);               \

@@ -23,7 +23,20 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def launch(world, backend, names, extra_env=None, timeout=180):
+def launch(world, backend, names, extra_env=None, timeout=180, attempts=3):
+    """Run the worker on `world` ranks.  Rendezvous hiccups (a port grabbed
+    between probing and binding, a slow peer) are retried on a fresh port; a
+    genuine failure fails every attempt."""
+    for attempt in range(attempts):
+        try:
+            return _launch_once(world, backend, names, extra_env, timeout)
+        except AssertionError as exc:
+            if attempt == attempts - 1:
+                raise
+            print(f"attempt {attempt + 1} failed, retrying on a fresh port:\n{str(exc)[-800:]}")
+
+
+def _launch_once(world, backend, names, extra_env, timeout):
     port = _free_port()
     procs = []
     for rank in range(world):
@@ -38,7 +51,7 @@ def launch(world, backend, names, extra_env=None, timeout=180):
         except subprocess.TimeoutExpired:
             for q in procs:
                 q.kill()
-            raise
+            raise AssertionError("rendezvous or run timed out")
         outs.append(out)
     if any(p.returncode != 0 for p in procs):
         raise AssertionError("\n".join(f"--- rank {r} (exit {p.returncode}) ---\n{o[-2500:]}"
