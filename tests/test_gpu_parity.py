@@ -169,9 +169,10 @@ def test_general_fused_kernel_without_star_specialisation():
         "print('ok')\n"
     ) % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
          os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "finite-difference_b200"))
-    env = dict(os.environ, FD_B200_NO_STAR="1")
-    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
-    assert out.returncode == 0 and out.stdout.strip().endswith("ok"), out.stdout + out.stderr
+    for switch in ("FD_B200_NO_STAR", "FD_B200_NO_LEAN"):   # general fused kernel; general star kernel
+        env = dict(os.environ, **{switch: "1"})
+        out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0 and out.stdout.strip().endswith("ok"), switch + out.stdout + out.stderr
 
 
 # ---------------------------------------------------------------- fp32 option
