@@ -24,8 +24,11 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   const DevFused<T>& F = P.F;
   const int n0 = F.n[0], n1 = F.n[1], n2 = F.n[2];
   const int nvec = n2 / VN;
-  const int vz0 = F.box_lo[2] / VN + blockIdx.x * (32 * VZ) + threadIdx.x;   // vector v sits 32 vectors further
-  const int y0 = F.box_lo[1] + (blockIdx.y * blockDim.y + threadIdx.y) * VY;
+  // 3-D: a block is 32 lanes along z by blockDim.y row groups; 2-D (one row per
+  // x plane): blockDim.y indexes further z groups instead
+  const int zgroup = HY ? blockIdx.x : blockIdx.x * blockDim.y + threadIdx.y;
+  const int vz0 = F.box_lo[2] / VN + zgroup * (32 * VZ) + threadIdx.x;   // vector v sits 32 vectors further
+  const int y0 = F.box_lo[1] + (HY ? (blockIdx.y * blockDim.y + threadIdx.y) * VY : blockIdx.y);
   const int x_begin = F.box_lo[0] + blockIdx.z * P.x_chunk;
   const int x_end = min(x_begin + P.x_chunk, F.box_hi[0]);
   const int plane = n1 * n2;
@@ -170,9 +173,9 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
       star_lean_kernel<T, R, true, 2, 1><<<grid, block, 0, stream>>>(P);
     } else {
       if (vecs % 64 != 0) return false;
-      int by = 4;
-      while (by > 1 && rows % by != 0) by >>= 1;
-      dim3 grid(vecs / 64, rows / by, gz), block(32, by, 1);
+      int by = 4;                                  // z groups per block
+      while (by > 1 && (vecs / 64) % by != 0) by >>= 1;
+      dim3 grid(vecs / 64 / by, rows, gz), block(32, by, 1);
       if (grid.y > 65535) return false;
       star_lean_kernel<T, R, false, 1, 2><<<grid, block, 0, stream>>>(P);
     }

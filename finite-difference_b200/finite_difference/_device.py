@@ -64,6 +64,8 @@ class Device:
         self.copy_stream = t.cuda.Stream(device=self.dev)
         # halo exchanges of a slab-decomposed model run here, ahead of the interior kernel
         self.comm_stream = t.cuda.Stream(device=self.dev, priority=-1)
+        # the thin rim slabs of a fixed-boundary statement run here, next to the interior box
+        self.rim_stream = t.cuda.Stream(device=self.dev, priority=-1)
 
     # -- streams ---------------------------------------------------------
     @property

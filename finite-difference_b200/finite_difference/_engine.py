@@ -358,10 +358,23 @@ class Engine:
         launch = self._fn["fd_fused_step"]
 
         def run(piece):
-            for box in self._split_boxes(d, piece):
+            boxes = self._split_boxes(d, piece)
+            rim_stream = self.dev.rim_stream if len(boxes) > 1 else None
+            if rim_stream is not None:
+                # the rim slabs read the same level and write disjoint points:
+                # they run beside the interior box instead of after it
+                start = self.dev.event()
+                start.record(self.dev.stream)
+                rim_stream.wait_event(start)
+            for i, box in enumerate(boxes):
                 for a in range(3):
                     d.box_lo[a], d.box_hi[a] = box[a]
-                nat.check(launch(C.byref(d), self.stream))
+                stream = rim_stream.cuda_stream if (i and rim_stream is not None) else self.stream
+                nat.check(launch(C.byref(d), stream))
+            if rim_stream is not None:
+                done = self.dev.event()
+                done.record(rim_stream)
+                self.dev.stream.wait_event(done)
 
         # (decided from facts every rank shares: slabs differ in size, collectives must not)
         eager = [ls for ls in levels if ls.H and ls.wants_ghosts and min(self.slab.counts) >= 3 * ls.H]

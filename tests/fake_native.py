@@ -244,6 +244,7 @@ class FakeDevice:
         self.dev = torch.device("cpu")
         self.copy_stream = None
         self.comm_stream = None
+        self.rim_stream = None
 
     stream = None
     stream_ptr = 0
