@@ -14,6 +14,9 @@ import numbers
 import numpy as np
 
 
+Field = None   # bound by field.py once the class exists (avoids a per-call import)
+
+
 class Node:
     """Expression node.  ``shape`` is the spatial shape (model order, time
     axis removed); ``dev`` caches the device tensor once evaluated."""
@@ -72,7 +75,8 @@ class Der(Node):
     def __init__(self, a, shape, axis, shifts, weights, scale, periodic, lo, hi, n_src, n_dst, stencil):
         super().__init__(shape)
         self.a, self.axis = a, axis
-        self.shifts, self.weights, self.scale = tuple(int(s) for s in shifts), tuple(weights), scale
+        self.shifts = tuple(shifts.tolist()) if hasattr(shifts, "tolist") else tuple(int(s) for s in shifts)
+        self.weights, self.scale = tuple(weights), scale
         self.periodic, self.lo, self.hi, self.n_src, self.n_dst = periodic, lo, hi, n_src, n_dst
         self.stencil = stencil
         self.slab = False   # True: along the axis that is decomposed over ranks
@@ -116,7 +120,6 @@ Dimension lengths: {dict(zip(self.model.axes_names,self.model.axes_lengths))}"
     # ---- arithmetic (FD.py:794-869) --------------------------------------
     @staticmethod
     def _operand(operand, models):
-        from .field import Field
         if isinstance(operand, Field):
             raise TypeError(
                 "Cannot perform arithmetic between a field and a field at a given moment -- use the new or prev properties for both fields")
@@ -165,12 +168,10 @@ Dimension lengths: {dict(zip(self.model.axes_names,self.model.axes_lengths))}"
         return FieldInstant._field_op(self, other, "mul")
 
     def __truediv__(self, other):
-        from .field import Field
         assert not isinstance(other, Field), "cannot divide by field"
         return FieldInstant._field_op(self, other, "truediv")
 
     def __pow__(self, other):
-        from .field import Field
         assert not isinstance(other, Field), "cannot raise to field"
         return FieldInstant._field_op(self, other, "pow")
 

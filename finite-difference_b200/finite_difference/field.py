@@ -347,6 +347,10 @@ class ConstantField(Field):
         self._set_expression(expression)
 
 
+_graph_module = __import__(__name__.rsplit(".", 1)[0] + "._graph", fromlist=["Field"])
+_graph_module.Field = Field
+
+
 def _pyplot():
     try:
         import matplotlib.pyplot as plt
