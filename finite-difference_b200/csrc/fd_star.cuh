@@ -12,14 +12,16 @@ namespace fdb {
 // MODE 0: canonical expression, unit spacing, every axis periodic (no range
 //         predicates, no faces)   1: canonical expression, unit spacing,
 //         any boundaries          2: everything decided at run time
-template <typename T, int R, int MODE>
+// 3 blocks per SM (<= 80 registers) where that does not spill: 3-point
+// stencils, and the 1-D / 2-D (y-marched) forms of the wider ones
+template <typename T, int R, int AXES>
 constexpr int star_min_blocks() {
-  return R <= 1 ? 3 : 2;
+  return (R <= 1 || AXES == 4 || AXES == 1) ? 3 : 2;
 }
 
 // VPT: 128-bit vectors per thread along z (1 or 2).  Two vectors halve the
 // z-halo loads and the per-iteration bookkeeping per point.
-template <typename T, int R, int AXES, int MODE, int VPT = 1, int OCC = star_min_blocks<T, R, MODE>()>
+template <typename T, int R, int AXES, int MODE, int VPT = 1, int OCC = star_min_blocks<T, R, AXES>()>
 __global__ void __launch_bounds__(256, OCC)
 star_kernel(const __grid_constant__ StarParams<T> P) {
   // AXES: 1 = {z}, 2 = {y,z}, 3 = {x,y,z}, 4 = {x,z} (x is the marched axis)
