@@ -366,6 +366,9 @@ class Engine:
             plan = self._build_fused_plan(dot_field, node, chain, t)
             if plan is None:
                 return False
+            if len(self._plans) >= 64:      # e.g. a coefficient that changes every step
+                self._plans.clear()
+                self._box_cache.clear()
             self._plans[key] = plan
         d, dot_state, levels, sources, dyn_faces, pad, dims3 = plan
         for src_state, offset, slab in sources:

@@ -9,6 +9,7 @@ Outputs
   tests/golden/der_cases.npz     random Stencil.der cases (inputs and outputs)
   tests/golden/der_cases.json    their parameters
   tests/golden/weights.json      Stencil weights table (FD.py:938-951)
+  tests/golden/misuse.json       exception type and message of every oracle/misuse_cases.py case
 """
 
 from __future__ import annotations
@@ -124,6 +125,18 @@ def main():
         table.append(dict(points=pts, order=order, weights=list(st.weights), text=buf.getvalue()))
     with open(os.path.join(GOLD, "weights.json"), "w") as fh:
         json.dump(table, fh, indent=0)
+    from oracle import misuse_cases
+    misuse = {}
+    for name, fn in misuse_cases.CASES.items():
+        try:
+            with contextlib.redirect_stdout(io.StringIO()):
+                fn(fd)
+            misuse[name] = None
+        except BaseException as exc:      # noqa: BLE001 - the type is what is being recorded
+            misuse[name] = [type(exc).__name__, str(exc)]
+    with open(os.path.join(GOLD, "misuse.json"), "w") as fh:
+        json.dump(misuse, fh, indent=0, sort_keys=True)
+    print(len(misuse), "misuse cases;", sum(v is None for v in misuse.values()), "did not raise in the reference")
     print("wrote", GOLD)
 
 

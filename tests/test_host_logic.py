@@ -95,3 +95,32 @@ def test_interior_rim_split_fake_native(shape):
         g.step += 1
     assert np.array_equal(got, S.data, equal_nan=True)
     assert np.array_equal(got_dot, Sd.data, equal_nan=True)
+
+
+def test_time_varying_coefficient_does_not_reuse_a_stale_plan():
+    """The launch descriptor is cached per statement; a scalar that changes from
+    step to step is part of the statement's key."""
+    import contextlib
+    import io
+    import numpy as np
+    from oracle import fd_numpy as O
+    n, n_t = 16, 6
+    ic = np.random.default_rng(5).random(n)
+    with fake_native.installed():
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model({"t": np.arange(n_t) * 0.01, "x": np.arange(n) * 1.0}, "t", periodic=("x",))
+            T = fd.Field(m, "T", n_time_ders=1)
+            d2 = fd.Stencil([-1, 0, 1], 2)
+            T.set_IC_values(ic)
+            while not m.finished:
+                T.dot.assign_update((0.1 + 0.05 * m.time_step) * d2.der(T.prev, "x"))
+                T.time_integrate_update()
+                m.increment_time()
+        got = T.data
+    want = np.full((n_t, n), np.nan)
+    want[0] = ic
+    w = O.stencil_weights([-1, 0, 1], 2)
+    for t in range(n_t - 1):
+        lap = O.der(want[t], [-1, 0, 1], w, 2, 0, True, False, False, 1.0)
+        want[t + 1] = want[t] + ((0.1 + 0.05 * t) * lap) * 0.01
+    assert np.array_equal(got, want)
