@@ -254,3 +254,15 @@ def test_fp32_heat_star_kernel(fd):
             m.increment_time()
     want, _ = O.run_heat(shape, 6, True, 0.1, 1e-3, ic32, dtype=np.float32)
     assert np.array_equal(T.data, want.astype(np.float64), equal_nan=True)
+
+
+def test_history_all_streams_every_level_correctly(fd):
+    """Default policy (every level of every field comes back, like the
+    reference) on a grid large enough that the device-to-host copies of a level
+    are still in flight when the ring slot is due to be overwritten."""
+    shape, n_t = (160, 128, 192), 10
+    ic = np.random.default_rng(41).random(shape)
+    m, T = _heat(fd, shape, n_t, True, 0.1, 1e-3, ic, history="all")
+    want, want_dot = O.run_heat(shape, n_t, True, 0.1, 1e-3, ic)
+    assert np.array_equal(T.data, want, equal_nan=True)
+    assert np.array_equal(T.dot.data, want_dot, equal_nan=True)
