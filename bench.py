@@ -50,6 +50,7 @@ WORKLOADS = {
 }
 DTYPES = {"c5": np.float32}
 K_DIFF, DT = 0.1, 1e-3
+GRID_SPACING = 1.0     # --dx: 1 (BASELINE synthetic inputs); other values exercise the scaled kernels
 
 
 # ------------------------------------------------------------------ helpers
@@ -132,7 +133,7 @@ def build_model(fd, workload, n_t, ic, history="last", world=1):
     names = ["x", "y", "z"][:len(shape)]
     axes = {"t": np.arange(n_t) * DT}
     for n, a in zip(shape, names):
-        axes[a] = np.arange(n) * 1.0
+        axes[a] = np.arange(n) * GRID_SPACING
     periodic = workload in ("c3", "c4", "c5")
     with contextlib.redirect_stdout(io.StringIO()):
         m = fd.Model(axes, "t", periodic=tuple(names) if periodic else (), history=history,
@@ -382,7 +383,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dx", type=float, default=1.0, help="grid spacing of every spatial axis (default 1, the benchmark definition)")
     args = ap.parse_args()
+    global GRID_SPACING
+    GRID_SPACING = args.dx
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference(args)

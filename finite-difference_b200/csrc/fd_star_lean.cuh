@@ -14,8 +14,17 @@
 
 namespace fdb {
 
-template <typename T, int R, bool HY, int VY, int VZ>
-__global__ void __launch_bounds__(128, 8)
+// SCALE: 0 = every axis divides by 1 (skipped), 1 = exact reciprocal multiply
+// (power-of-two spacing), 3 = FMA-corrected division by the invariant dx**order.
+template <typename T, int SCALE>
+__device__ __forceinline__ T lean_scale(T v, const StarAxis<T>& a) {
+  if (SCALE == 0) return v;
+  if (SCALE == 1) return mul_rn(v, a.inv);
+  return div_invariant(v, a.scale, a.inv);
+}
+
+template <typename T, int R, bool HY, int VY, int VZ, int SCALE>
+__global__ void __launch_bounds__(128, SCALE == 3 ? 6 : 8)
 star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   constexpr int VN = Vec<T>::N;
   constexpr int NP = 2 * R + 1;
@@ -106,10 +115,12 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
           T dz = (T)0;
 #pragma unroll
           for (int p = 0; p < NP; ++p) dz = add_rn(dz, mul_rn(az.w[p], zw[e + p]));
+          dz = lean_scale<T, SCALE>(dz, az);
           saw_inf |= is_inf(dz);
           T dx = (T)0;
 #pragma unroll
           for (int p = 0; p < NP; ++p) dx = add_rn(dx, mul_rn(ax.w[p], win[p][r][v].v[e]));
+          dx = lean_scale<T, SCALE>(dx, ax);
           saw_inf |= is_inf(dx);
           T total;
           if (HY) {
@@ -121,6 +132,7 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
                                    : (rr >= VY ? hp[rr >= VY ? rr - VY : 0][v].v[e] : win[R][rr < 0 ? 0 : (rr >= VY ? 0 : rr)][v].v[e]);
               dy = add_rn(dy, mul_rn(ay.w[p], f));
             }
+            dy = lean_scale<T, SCALE>(dy, ay);
             saw_inf |= is_inf(dy);
             total = add_rn(add_rn(dx, dy), dz);
           } else {
@@ -156,6 +168,7 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
   } else {
     const DevFused<T>& F = P.F;
     if (mode != 0 || F.depth != 1 || !P.prev_is_src[0] || F.dot_out || (axes != 3 && axes != 4)) return false;
+    if (P.scale_class == 2) return false;                      // IEEE division somewhere: general kernel
     const int rows = F.box_hi[1] - F.box_lo[1], vecs = (F.box_hi[2] - F.box_lo[2]) / VN, nx = F.box_hi[0] - F.box_lo[0];
     if (rows <= 0 || vecs <= 0 || nx <= 0) return false;
     if (F.box_lo[2] % VN != 0 || F.box_hi[2] % VN != 0) return false;
@@ -170,14 +183,24 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
       while (by > 1 && (rows / 2) % by != 0) by >>= 1;
       dim3 grid(vecs / 32, rows / (2 * by), gz), block(32, by, 1);
       if (grid.y > 65535) return false;
-      star_lean_kernel<T, R, true, 2, 1><<<grid, block, 0, stream>>>(P);
+      if (P.scale_class == 0)
+        star_lean_kernel<T, R, true, 2, 1, 0><<<grid, block, 0, stream>>>(P);
+      else if (P.scale_class == 1)
+        star_lean_kernel<T, R, true, 2, 1, 1><<<grid, block, 0, stream>>>(P);
+      else
+        star_lean_kernel<T, R, true, 2, 1, 3><<<grid, block, 0, stream>>>(P);
     } else {
       if (vecs % 64 != 0) return false;
       int by = 4;                                  // z groups per block
       while (by > 1 && (vecs / 64) % by != 0) by >>= 1;
       dim3 grid(vecs / 64 / by, rows, gz), block(32, by, 1);
       if (grid.y > 65535) return false;
-      star_lean_kernel<T, R, false, 1, 2><<<grid, block, 0, stream>>>(P);
+      if (P.scale_class == 0)
+        star_lean_kernel<T, R, false, 1, 2, 0><<<grid, block, 0, stream>>>(P);
+      else if (P.scale_class == 1)
+        star_lean_kernel<T, R, false, 1, 2, 1><<<grid, block, 0, stream>>>(P);
+      else
+        star_lean_kernel<T, R, false, 1, 2, 3><<<grid, block, 0, stream>>>(P);
     }
     return true;
   }

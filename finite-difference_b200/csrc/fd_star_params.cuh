@@ -41,6 +41,7 @@ struct StarParams {
   int32_t subtract[3], negate[3], has_pre[3];
   T pre[3];
   int32_t nterms, x_chunk, has_mul;
+  int32_t scale_class;   // 0: every axis divides by 1; 1: exact reciprocal multiplies; 3: FMA-corrected; 2: IEEE division somewhere
   int32_t prev_is_src[2];
   T mul;
 };
@@ -112,7 +113,8 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
   P->src = t0.src;
   P->nterms = F.nterms;
   const int naxes = F.nterms;
-  bool canonical = true, unit = true;
+  bool canonical = true;
+  int scale_class = 0;
   for (int k = 0; k < 3; ++k) {
     P->order[k] = 2;
     P->subtract[k] = P->negate[k] = P->has_pre[k] = 0;
@@ -129,7 +131,13 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
     A.periodic = t.periodic;
     A.lo = t.lo;
     A.hi = t.hi;
-    if (k >= 0 && t.st.div_mode != 0) unit = false;
+    if (k >= 0) {
+      const int m = t.st.div_mode;
+      if (m == 2 || scale_class == 2)
+        scale_class = 2;
+      else if (m > scale_class)
+        scale_class = m;     // 0 < 1 < 3
+    }
   }
   for (int k = 0; k < F.nterms; ++k) {
     const DevTerm<T>& t = F.term[k];
@@ -163,7 +171,8 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
       if (F.face[l][a][0] && F.box_lo[a] <= F.rim_lo[a] && F.rim_lo[a] < F.box_hi[a]) clean = false;
       if (F.face[l][a][1] && F.box_lo[a] <= F.rim_hi[a] && F.rim_hi[a] < F.box_hi[a]) clean = false;
     }
-  *mode = (canonical && unit && simple_post) ? (clean ? 0 : 1) : 2;
+  P->scale_class = scale_class;
+  *mode = (canonical && simple_post) ? (clean ? 0 : 1) : 2;
   return true;
 }
 

@@ -56,7 +56,9 @@ typedef struct fd_stencil {
   int32_t shifts[FD_MAX_POINTS];
   double weights[FD_MAX_POINTS];
   double scale;
-  int32_t exact_div; /* 1: divide (bit-exact); 0: multiply by 1/scale       */
+  int32_t exact_div; /* 1: bit-exact quotient (the library picks the cheapest
+                        exact method); 0: multiply by 1/scale (<= 1 ulp off);
+                        2: force the IEEE division instruction sequence       */
 } fd_stencil_t;
 
 /* element-wise operations of FieldInstant arithmetic (FD.py:794-869) */

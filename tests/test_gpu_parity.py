@@ -266,3 +266,38 @@ def test_history_all_streams_every_level_correctly(fd):
     want, want_dot = O.run_heat(shape, n_t, True, 0.1, 1e-3, ic)
     assert np.array_equal(T.data, want, equal_nan=True)
     assert np.array_equal(T.dot.data, want_dot, equal_nan=True)
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_invariant_division_is_correctly_rounded(dtype):
+    """The FMA-corrected reciprocal division (exact_div=1, div_mode 3) against
+    the IEEE division sequence (exact_div=2) on ~10^7 values per divisor,
+    including zeros, infinities, NaN, subnormals and huge magnitudes."""
+    import torch
+    import finite_difference._native as nat
+    rng = np.random.default_rng(77)
+    n = 1 << 20
+    mags = rng.uniform(-300 if dtype == np.float64 else -37, 300 if dtype == np.float64 else 37, n)
+    x = (rng.standard_normal(n) * 10.0 ** mags).astype(dtype)
+    x[:16] = [0.0, -0.0, np.inf, -np.inf, np.nan, 5e-324, -5e-324, 1e-310, 1.0, -1.0, 3.0, 1e308, -1e308, 2.0 ** -1022, 0.1, 7.0]
+    more = rng.standard_normal(n).astype(dtype)
+    tdt = torch.float64 if dtype == np.float64 else torch.float32
+    fn = nat.lib.fd_der_f64 if dtype == np.float64 else nat.lib.fd_der_f32
+    flags = torch.zeros(nat.FD_NUM_FLAGS, dtype=torch.int64, device="cuda")
+    for scale in [0.1, 0.01, 0.3, 3.0, 7.0, 1e-3, 1.0 / 3.0, 0.09, 0.010000000000000002, 1e-6, 12345.678, 0.7 ** 2,
+                  -0.3, 1e8]:
+        for vals in (x, more):
+            src = torch.from_numpy(vals.copy()).cuda()
+            outs = []
+            for exact in (1, 2):
+                st = nat.make_stencil([0], [1.0], scale)
+                st.exact_div = exact
+                dst = torch.empty(n, dtype=tdt, device="cuda")
+                nat.check(fn(dst.data_ptr(), src.data_ptr(), 1, n, n, 1, C.byref(st), 1, 0, n, flags.data_ptr(), 0))
+                outs.append(dst.cpu().numpy())
+            same = (outs[0].view(np.uint64 if dtype == np.float64 else np.uint32) ==
+                    outs[1].view(np.uint64 if dtype == np.float64 else np.uint32)) | (np.isnan(outs[0]) & np.isnan(outs[1]))
+            assert same.all(), (scale, vals[~same][:5], outs[0][~same][:5], outs[1][~same][:5])
+            with np.errstate(all="ignore"):
+                want = vals / dtype(scale)
+            assert np.array_equal(outs[0], want, equal_nan=True), scale
