@@ -23,8 +23,11 @@ __device__ __forceinline__ T lean_scale(T v, const StarAxis<T>& a) {
   return div_invariant(v, a.scale, a.inv);
 }
 
-template <typename T, int R, bool HY, int VY, int VZ, int SCALE>
-__global__ void __launch_bounds__(128, SCALE == 3 ? 6 : 8)
+// BZ: the contiguous axis is a fixed axis inside the box: outputs outside its
+// [lo, hi) are NaN and its two boundary faces are merged here (a z rim cannot be
+// peeled off as a thin slab without giving up whole 128-bit vector groups).
+template <typename T, int R, bool HY, int VY, int VZ, int SCALE, bool BZ>
+__global__ void __launch_bounds__(128, (SCALE == 3 || BZ) ? 6 : 8)
 star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   constexpr int VN = Vec<T>::N;
   constexpr int NP = 2 * R + 1;
@@ -45,118 +48,154 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   const StarAxis<T>& ay = P.ax[1];
   const StarAxis<T>& az = P.ax[2];
   unsigned nan_cnt = 0;
-  bool saw_inf = false;
+  bool saw_inf = false, clash = false;
+  // the launch tiles the box exactly except for the last vector group of a row
+  // (VZ == 1 only) and the last row group
+  const bool active = (vz0 + 32 * (VZ - 1) < F.box_hi[2] / VN) && (y0 + VY <= F.box_hi[1]);
 
-  // neighbour offsets (elements) relative to (x, y0, vz0*VN)
-  int zl[VZ], zr[VZ];
+  if (active) {
+    // neighbour offsets (elements) relative to (x, y0, vz0*VN)
+    int zl[VZ], zr[VZ];
 #pragma unroll
-  for (int v = 0; v < VZ; ++v) {
-    zl[v] = (wrap_or_clamp(vz0 + 32 * v - 1, nvec, az.periodic) - vz0) * VN;
-    zr[v] = (wrap_or_clamp(vz0 + 32 * v + 1, nvec, az.periodic) - vz0) * VN;
-  }
-  int oym[HY ? R : 1], oyp[HY ? R : 1];
-  if (HY) {
-#pragma unroll
-    for (int k = 0; k < R; ++k) {
-      oym[k] = (wrap_or_clamp(y0 - 1 - k, n1, ay.periodic) - y0) * n2;
-      oyp[k] = (wrap_or_clamp(y0 + VY + k, n1, ay.periodic) - y0) * n2;
+    for (int v = 0; v < VZ; ++v) {
+      zl[v] = (wrap_or_clamp(vz0 + 32 * v - 1, nvec, az.periodic) - vz0) * VN;
+      zr[v] = (wrap_or_clamp(vz0 + 32 * v + 1, nvec, az.periodic) - vz0) * VN;
     }
-  }
-  const T* col = P.src + (int64_t)y0 * n2 + (int64_t)vz0 * VN;
-  // x window: planes x-R .. x+R in use, x+R+1 prefetched
-  PK win[NP + 1][VY][VZ];
-  auto load_plane = [&](PK (&w)[VY][VZ], int x) {
-    const T* p = col + (int64_t)wrap_or_clamp(x, n0, ax.periodic) * plane;
-#pragma unroll
-    for (int r = 0; r < VY; ++r)
-#pragma unroll
-      for (int v = 0; v < VZ; ++v) w[r][v] = load_vec<T>(p + r * n2 + 32 * VN * v);
-  };
-#pragma unroll
-  for (int p = 0; p < NP; ++p) load_plane(win[p], x_begin - R + p);
-  const T* here = col + (int64_t)x_begin * plane;
-  T* outp = F.out[0] + (int64_t)x_begin * plane + (int64_t)y0 * n2 + (int64_t)vz0 * VN;
-
-  for (int x = x_begin; x < x_end; ++x) {
-    load_plane(win[NP], x + R + 1);
-    PK hm[HY ? R : 1][VZ], hp[HY ? R : 1][VZ];     // rows below / above the thread's rows
+    int oym[HY ? R : 1], oyp[HY ? R : 1];
     if (HY) {
 #pragma unroll
-      for (int k = 0; k < R; ++k)
-#pragma unroll
-        for (int v = 0; v < VZ; ++v) {
-          hm[k][v] = load_vec<T>(here + oym[k] + 32 * VN * v);
-          hp[k][v] = load_vec<T>(here + oyp[k] + 32 * VN * v);
-        }
-    }
-#pragma unroll
-    for (int r = 0; r < VY; ++r) {
-#pragma unroll
-      for (int v = 0; v < VZ; ++v) {
-        const PK c = win[R][r][v];
-        // z window: R elements | the vector | R elements
-        T zw[VN + 2 * R];
-        if (R == 1) {
-          zw[0] = __ldg(here + r * n2 + zl[v] + VN - 1);
-          zw[VN + 1] = __ldg(here + r * n2 + zr[v]);
-        } else {
-          const PK l = load_vec<T>(here + r * n2 + zl[v]), rr = load_vec<T>(here + r * n2 + zr[v]);
-#pragma unroll
-          for (int k = 0; k < R; ++k) {
-            zw[k] = l.v[VN - R + k];
-            zw[VN + R + k] = rr.v[k];
-          }
-        }
-#pragma unroll
-        for (int e = 0; e < VN; ++e) zw[R + e] = c.v[e];
-        PK res;
-#pragma unroll
-        for (int e = 0; e < VN; ++e) {
-          T dz = (T)0;
-#pragma unroll
-          for (int p = 0; p < NP; ++p) dz = add_rn(dz, mul_rn(az.w[p], zw[e + p]));
-          dz = lean_scale<T, SCALE>(dz, az);
-          saw_inf |= is_inf(dz);
-          T dx = (T)0;
-#pragma unroll
-          for (int p = 0; p < NP; ++p) dx = add_rn(dx, mul_rn(ax.w[p], win[p][r][v].v[e]));
-          dx = lean_scale<T, SCALE>(dx, ax);
-          saw_inf |= is_inf(dx);
-          T total;
-          if (HY) {
-            T dy = (T)0;
-#pragma unroll
-            for (int p = 0; p < NP; ++p) {
-              const int rr = r + p - R;          // row offset within the thread's rows
-              const T f = (rr < 0) ? hm[rr < 0 ? -rr - 1 : 0][v].v[e]
-                                   : (rr >= VY ? hp[rr >= VY ? rr - VY : 0][v].v[e] : win[R][rr < 0 ? 0 : (rr >= VY ? 0 : rr)][v].v[e]);
-              dy = add_rn(dy, mul_rn(ay.w[p], f));
-            }
-            dy = lean_scale<T, SCALE>(dy, ay);
-            saw_inf |= is_inf(dy);
-            total = add_rn(add_rn(dx, dy), dz);
-          } else {
-            total = add_rn(dx, dz);
-          }
-          total = mul_rn(total, P.mul);
-          const T nv = add_rn(c.v[e], mul_rn(total, F.dt));
-          nan_cnt += is_nan(nv) ? 1u : 0u;
-          res.v[e] = nv;
-        }
-        store_vec<T>(outp + r * n2 + 32 * VN * v, res);
+      for (int k = 0; k < R; ++k) {
+        oym[k] = (wrap_or_clamp(y0 - 1 - k, n1, ay.periodic) - y0) * n2;
+        oyp[k] = (wrap_or_clamp(y0 + VY + k, n1, ay.periodic) - y0) * n2;
       }
     }
-    here += plane;
-    outp += plane;
-#pragma unroll
-    for (int p = 0; p < NP; ++p)
+    const T* col = P.src + (int64_t)y0 * n2 + (int64_t)vz0 * VN;
+    // x window: planes x-R .. x+R in use, x+R+1 prefetched
+    PK win[NP + 1][VY][VZ];
+    auto load_plane = [&](PK (&w)[VY][VZ], int x) {
+      const T* p = col + (int64_t)wrap_or_clamp(x, n0, ax.periodic) * plane;
 #pragma unroll
       for (int r = 0; r < VY; ++r)
 #pragma unroll
-        for (int v = 0; v < VZ; ++v) win[p][r][v] = win[p + 1][r][v];
+        for (int v = 0; v < VZ; ++v) w[r][v] = load_vec<T>(p + r * n2 + 32 * VN * v);
+    };
+#pragma unroll
+    for (int p = 0; p < NP; ++p) load_plane(win[p], x_begin - R + p);
+    const T* here = col + (int64_t)x_begin * plane;
+    T* outp = F.out[0] + (int64_t)x_begin * plane + (int64_t)y0 * n2 + (int64_t)vz0 * VN;
+
+    for (int x = x_begin; x < x_end; ++x) {
+      load_plane(win[NP], x + R + 1);
+      PK hm[HY ? R : 1][VZ], hp[HY ? R : 1][VZ];     // rows below / above the thread's rows
+      if (HY) {
+#pragma unroll
+        for (int k = 0; k < R; ++k)
+#pragma unroll
+          for (int v = 0; v < VZ; ++v) {
+            hm[k][v] = load_vec<T>(here + oym[k] + 32 * VN * v);
+            hp[k][v] = load_vec<T>(here + oyp[k] + 32 * VN * v);
+          }
+      }
+#pragma unroll
+      for (int r = 0; r < VY; ++r) {
+#pragma unroll
+        for (int v = 0; v < VZ; ++v) {
+          const PK c = win[R][r][v];
+          // z window: R elements | the vector | R elements
+          T zw[VN + 2 * R];
+          if (R == 1) {
+            zw[0] = __ldg(here + r * n2 + zl[v] + VN - 1);
+            zw[VN + 1] = __ldg(here + r * n2 + zr[v]);
+          } else {
+            const PK l = load_vec<T>(here + r * n2 + zl[v]), rr = load_vec<T>(here + r * n2 + zr[v]);
+#pragma unroll
+            for (int k = 0; k < R; ++k) {
+              zw[k] = l.v[VN - R + k];
+              zw[VN + R + k] = rr.v[k];
+            }
+          }
+#pragma unroll
+          for (int e = 0; e < VN; ++e) zw[R + e] = c.v[e];
+          PK res;
+#pragma unroll
+          for (int e = 0; e < VN; ++e) {
+            const int j2 = (vz0 + 32 * v) * VN + e;          // global index along z
+            T dz = (T)0;
+#pragma unroll
+            for (int p = 0; p < NP; ++p) dz = add_rn(dz, mul_rn(az.w[p], zw[e + p]));
+            dz = lean_scale<T, SCALE>(dz, az);
+            if (BZ && (j2 < az.lo || j2 >= az.hi)) dz = quiet_nan<T>();
+            saw_inf |= is_inf(dz);
+            T dx = (T)0;
+#pragma unroll
+            for (int p = 0; p < NP; ++p) dx = add_rn(dx, mul_rn(ax.w[p], win[p][r][v].v[e]));
+            dx = lean_scale<T, SCALE>(dx, ax);
+            saw_inf |= is_inf(dx);
+            T total;
+            if (HY) {
+              T dy = (T)0;
+#pragma unroll
+              for (int p = 0; p < NP; ++p) {
+                const int rr = r + p - R;          // row offset within the thread's rows
+                const T f = (rr < 0) ? hm[rr < 0 ? -rr - 1 : 0][v].v[e]
+                                     : (rr >= VY ? hp[rr >= VY ? rr - VY : 0][v].v[e] : win[R][rr < 0 ? 0 : (rr >= VY ? 0 : rr)][v].v[e]);
+                dy = add_rn(dy, mul_rn(ay.w[p], f));
+              }
+              dy = lean_scale<T, SCALE>(dy, ay);
+              saw_inf |= is_inf(dy);
+              total = add_rn(add_rn(dx, dy), dz);
+            } else {
+              total = add_rn(dx, dz);
+            }
+            total = mul_rn(total, P.mul);
+            T nv = add_rn(c.v[e], mul_rn(total, F.dt));
+            if (BZ && (j2 == F.rim_lo[2] || j2 == F.rim_hi[2])) {
+              // boundary face of the contiguous axis (FD.py:541-576)
+              const T* face = F.face[0][2][j2 == F.rim_lo[2] ? 0 : 1];
+              if (face) {
+                const T stored = face[(int64_t)x * n1 + y0 + r];
+                if (is_nan(nv))
+                  nv = stored;
+                else
+                  clash |= !is_nan(stored);
+              }
+            }
+            nan_cnt += is_nan(nv) ? 1u : 0u;
+            res.v[e] = nv;
+          }
+          store_vec<T>(outp + r * n2 + 32 * VN * v, res);
+        }
+      }
+      here += plane;
+      outp += plane;
+#pragma unroll
+      for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < VY; ++r)
+#pragma unroll
+          for (int v = 0; v < VZ; ++v) win[p][r][v] = win[p + 1][r][v];
+    }
   }
   if (saw_inf) raise_flag(F.flags, FD_FLAG_INF);
+  if (BZ && clash) raise_flag(F.flags, FD_FLAG_OVERRIDE);
   warp_add_count(F.nan_count[0], nan_cnt);
+}
+
+template <typename T, int R, bool HY, int VY, int VZ>
+static void launch_lean(StarParams<T>& P, dim3 grid, dim3 block, bool bz, cudaStream_t stream) {
+#define FD_LEAN(SC)                                                                 \
+  if (bz)                                                                           \
+    star_lean_kernel<T, R, HY, VY, VZ, SC, true><<<grid, block, 0, stream>>>(P);    \
+  else                                                                              \
+    star_lean_kernel<T, R, HY, VY, VZ, SC, false><<<grid, block, 0, stream>>>(P);
+  if (P.scale_class == 0) {
+    FD_LEAN(0)
+  } else if (P.scale_class == 1) {
+    FD_LEAN(1)
+  } else {
+    FD_LEAN(3)
+  }
+#undef FD_LEAN
 }
 
 // Launch the lean kernel if the statement qualifies; returns false otherwise.
@@ -167,7 +206,8 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
     return false;
   } else {
     const DevFused<T>& F = P.F;
-    if (mode != 0 || F.depth != 1 || !P.prev_is_src[0] || F.dot_out || (axes != 3 && axes != 4)) return false;
+    const bool bz = mode == 1 && P.only_z_bounded;          // clean in x and y, fixed along z
+    if (!(mode == 0 || bz) || F.depth != 1 || !P.prev_is_src[0] || F.dot_out || (axes != 3 && axes != 4)) return false;
     if (P.scale_class == 2) return false;                      // IEEE division somewhere: general kernel
     const int rows = F.box_hi[1] - F.box_lo[1], vecs = (F.box_hi[2] - F.box_lo[2]) / VN, nx = F.box_hi[0] - F.box_lo[0];
     if (rows <= 0 || vecs <= 0 || nx <= 0) return false;
@@ -176,31 +216,33 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
     if (const int forced = tuning_chunk()) chunk = forced;
     P.x_chunk = chunk;
     const unsigned gz = (nx + chunk - 1) / chunk;
-    if (gz > 65535) return false;
+    if (gz > 65535 || vecs < 3) return false;
     if (axes == 3) {
-      if (rows % 2 != 0 || vecs % 32 != 0 || rows < 2 * R || F.n[1] < 2 + 2 * R) return false;
+      if (F.n[1] < 2 + 2 * R) return false;
+      const int vy = rows % 2 == 0 ? 2 : 1;                   // rows per thread
+      const int groups = rows / vy;
       int by = 4;
-      while (by > 1 && (rows / 2) % by != 0) by >>= 1;
-      dim3 grid(vecs / 32, rows / (2 * by), gz), block(32, by, 1);
+      while (by > 1 && groups % by != 0) by >>= 1;
+      dim3 grid((vecs + 31) / 32, groups / by, gz), block(32, by, 1);
       if (grid.y > 65535) return false;
-      if (P.scale_class == 0)
-        star_lean_kernel<T, R, true, 2, 1, 0><<<grid, block, 0, stream>>>(P);
-      else if (P.scale_class == 1)
-        star_lean_kernel<T, R, true, 2, 1, 1><<<grid, block, 0, stream>>>(P);
+      if (vy == 2)
+        launch_lean<T, R, true, 2, 1>(P, grid, block, bz, stream);
       else
-        star_lean_kernel<T, R, true, 2, 1, 3><<<grid, block, 0, stream>>>(P);
+        launch_lean<T, R, true, 1, 1>(P, grid, block, bz, stream);
     } else {
-      if (vecs % 64 != 0) return false;
-      int by = 4;                                  // z groups per block
-      while (by > 1 && (vecs / 64) % by != 0) by >>= 1;
-      dim3 grid(vecs / 64 / by, rows, gz), block(32, by, 1);
-      if (grid.y > 65535) return false;
-      if (P.scale_class == 0)
-        star_lean_kernel<T, R, false, 1, 2, 0><<<grid, block, 0, stream>>>(P);
-      else if (P.scale_class == 1)
-        star_lean_kernel<T, R, false, 1, 2, 1><<<grid, block, 0, stream>>>(P);
-      else
-        star_lean_kernel<T, R, false, 1, 2, 3><<<grid, block, 0, stream>>>(P);
+      if (rows > 65535) return false;
+      if (vecs % 64 == 0) {
+        int by = 4;                                  // z groups per block
+        while (by > 1 && (vecs / 64) % by != 0) by >>= 1;
+        dim3 grid(vecs / 64 / by, rows, gz), block(32, by, 1);
+        launch_lean<T, R, false, 1, 2>(P, grid, block, bz, stream);
+      } else {
+        const int groups = (vecs + 31) / 32;
+        int by = 4;
+        while (by > 1 && groups % by != 0) by >>= 1;
+        dim3 grid(groups / by, rows, gz), block(32, by, 1);
+        launch_lean<T, R, false, 1, 1>(P, grid, block, bz, stream);
+      }
     }
     return true;
   }

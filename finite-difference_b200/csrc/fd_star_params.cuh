@@ -41,6 +41,7 @@ struct StarParams {
   int32_t subtract[3], negate[3], has_pre[3];
   T pre[3];
   int32_t nterms, x_chunk, has_mul;
+  int32_t only_z_bounded;   // the box is clean along x and y; only the contiguous axis has a rim in it
   int32_t scale_class;   // 0: every axis divides by 1; 1: exact reciprocal multiplies; 3: FMA-corrected; 2: IEEE division somewhere
   int32_t prev_is_src[2];
   T mul;
@@ -161,16 +162,24 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
   *axes = axes_code;
   // "clean" box: no output in it is outside a term's [lo, hi) and no boundary
   // face touches it, so the predicate-free instantiation is exact there
-  bool clean = true;
+  bool clean = true, clean_xy = true;
   for (int k = 0; k < F.nterms; ++k) {
     const DevTerm<T>& t = F.term[k];
-    if (!t.periodic && (F.box_lo[t.axis] < t.lo || F.box_hi[t.axis] > t.hi)) clean = false;
+    if (!t.periodic && (F.box_lo[t.axis] < t.lo || F.box_hi[t.axis] > t.hi)) {
+      clean = false;
+      if (t.axis != 2) clean_xy = false;
+    }
   }
   for (int a = 0; a < 3; ++a)
     for (int l = 0; l < F.depth; ++l) {
-      if (F.face[l][a][0] && F.box_lo[a] <= F.rim_lo[a] && F.rim_lo[a] < F.box_hi[a]) clean = false;
-      if (F.face[l][a][1] && F.box_lo[a] <= F.rim_hi[a] && F.rim_hi[a] < F.box_hi[a]) clean = false;
+      const bool lo_in = F.face[l][a][0] && F.box_lo[a] <= F.rim_lo[a] && F.rim_lo[a] < F.box_hi[a];
+      const bool hi_in = F.face[l][a][1] && F.box_lo[a] <= F.rim_hi[a] && F.rim_hi[a] < F.box_hi[a];
+      if (lo_in || hi_in) {
+        clean = false;
+        if (a != 2) clean_xy = false;
+      }
     }
+  P->only_z_bounded = (!clean && clean_xy) ? 1 : 0;
   P->scale_class = scale_class;
   *mode = (canonical && simple_post) ? (clean ? 0 : 1) : 2;
   return true;

@@ -480,7 +480,11 @@ class Engine:
                     inner[a][1] = min(inner[a][1], d.rim_hi[a])
         if inner == region:
             return [region]
-        # the contiguous axis is processed in whole vector groups
+        # 3-point statements: the kernels handle a fixed contiguous axis themselves
+        # (a z rim would cost whole vector groups: 2 x 128 of 512 points)
+        if all(d.term[k].st.npts == 3 for k in range(d.nterms)) and d.depth == 1:
+            inner[2] = list(region[2])
+        # otherwise the contiguous axis is processed in whole vector groups
         align = 64 * (16 // self.dtype.itemsize)
         if inner[2] != region[2]:
             lo = -(-inner[2][0] // align) * align
@@ -939,9 +943,13 @@ def _match_statement(node):
     while True:
         terms = _match_sum(node)
         if terms is not None:
-            # a lone `der*scalar` term is equally a post-multiplication; either
-            # reading rounds identically
             posts.reverse()
+            if len(terms) == 1 and terms[0][2] is not None and not terms[0][3]:
+                # a lone `der*c` is equally a post-multiplication (same rounding);
+                # that reading is the kernels' canonical form
+                der, subtract, pre, negate = terms[0]
+                terms = [(der, subtract, None, negate)]
+                posts.insert(0, (nat.POST_MUL, pre, None))
             return terms, posts
         if isinstance(node, Unary):
             posts.append((nat.POST_NEG, None, None))

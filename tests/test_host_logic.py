@@ -77,7 +77,9 @@ def test_interior_rim_split_fake_native(shape):
                 T.time_integrate_update()
                 m.increment_time()
         got, got_dot = T.data, T.dot.data
-        assert fake.launches >= 3 * 4   # interior + rim slabs per step (the NaN count of the IC adds one)
+        # interior box + the rim slabs of the non-contiguous axes per step (3-point
+        # stencils: the contiguous axis' rim is handled inside the kernels)
+        assert fake.launches >= 3 * (1 + 2 * (len(shape) - 1))
     # oracle with the same boundary values
     g = O.Grid(axes, "t")
     S, Sd = O.Series(g), O.Series(g)
