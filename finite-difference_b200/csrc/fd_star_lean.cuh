@@ -213,6 +213,11 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
     if (rows <= 0 || vecs <= 0 || nx <= 0) return false;
     if (F.box_lo[2] % VN != 0 || F.box_hi[2] % VN != 0) return false;
     int chunk = 8;
+    {
+      // small grids: shorter marches so that every SM still gets several blocks
+      const int64_t tiles = (int64_t)((vecs + 31) / 32) * ((rows + 7) / 8);
+      while (chunk > 1 && tiles * ((nx + chunk - 1) / chunk) < 148 * 8) chunk >>= 1;
+    }
     if (const int forced = tuning_chunk()) chunk = forced;
     P.x_chunk = chunk;
     const unsigned gz = (nx + chunk - 1) / chunk;
@@ -221,9 +226,9 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
       if (F.n[1] < 2 + 2 * R) return false;
       const int vy = rows % 2 == 0 ? 2 : 1;                   // rows per thread
       const int groups = rows / vy;
-      int by = 4;
-      while (by > 1 && groups % by != 0) by >>= 1;
-      dim3 grid((vecs + 31) / 32, groups / by, gz), block(32, by, 1);
+      int by = 4;                                  // row groups per block; the last block may be partial
+      while (by > 1 && by / 2 >= groups) by >>= 1;
+      dim3 grid((vecs + 31) / 32, (groups + by - 1) / by, gz), block(32, by, 1);
       if (grid.y > 65535) return false;
       if (vy == 2)
         launch_lean<T, R, true, 2, 1>(P, grid, block, bz, stream);
@@ -232,15 +237,16 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
     } else {
       if (rows > 65535) return false;
       if (vecs % 64 == 0) {
-        int by = 4;                                  // z groups per block
-        while (by > 1 && (vecs / 64) % by != 0) by >>= 1;
-        dim3 grid(vecs / 64 / by, rows, gz), block(32, by, 1);
+        const int groups = vecs / 64;
+        int by = 4;                                  // z groups per block; the last block may be partial
+        while (by > 1 && by / 2 >= groups) by >>= 1;
+        dim3 grid((groups + by - 1) / by, rows, gz), block(32, by, 1);
         launch_lean<T, R, false, 1, 2>(P, grid, block, bz, stream);
       } else {
         const int groups = (vecs + 31) / 32;
         int by = 4;
-        while (by > 1 && groups % by != 0) by >>= 1;
-        dim3 grid(groups / by, rows, gz), block(32, by, 1);
+        while (by > 1 && by / 2 >= groups) by >>= 1;
+        dim3 grid((groups + by - 1) / by, rows, gz), block(32, by, 1);
         launch_lean<T, R, false, 1, 1>(P, grid, block, bz, stream);
       }
     }

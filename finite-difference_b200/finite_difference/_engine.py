@@ -192,7 +192,7 @@ class Engine:
         self.overlap = os.environ.get("FD_B200_NO_OVERLAP", "0") != "1"
         self.fuse_pairs = os.environ.get("FD_B200_NO_PAIR", "0") != "1"
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
-        default_poll = 1 if points < (1 << 20) else 64
+        default_poll = 16 if points < (1 << 20) else 64
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
         self.last_poll = model.time_step
         self.pending_copies = []          # [(state, slot, t, host tensor, event)]

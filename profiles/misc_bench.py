@@ -65,6 +65,10 @@ CASES = [
     ("3-D 384^3 periodic radius 4", (384, 384, 384), True, 1.0, "k*(sum)", 4),
     ("3-D 64^3 periodic (launch-bound)", (64, 64, 64), True, 1.0, "k*(sum)", 1),
 ]
+import os as _os
+_only = _os.environ.get("MISC_ONLY")
 for name, shape, periodic, dx, form, radius in CASES:
+    if _only and _only not in name:
+        continue
     ms, gbs, stats = heat(shape, periodic, dx, form=form, radius=radius)
     print(f"{name:40s} {ms:8.4f} ms/step  {gbs:7.0f} GB/s algorithmic  {stats}")
