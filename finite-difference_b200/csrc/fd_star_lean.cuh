@@ -26,8 +26,9 @@ __device__ __forceinline__ T lean_scale(T v, const StarAxis<T>& a) {
 // BZ: the contiguous axis is a fixed axis inside the box: outputs outside its
 // [lo, hi) are NaN and its two boundary faces are merged here (a z rim cannot be
 // peeled off as a thin slab without giving up whole 128-bit vector groups).
-template <typename T, int R, bool HY, int VY, int VZ, int SCALE, bool BZ>
-__global__ void __launch_bounds__(128, (SCALE == 3 || BZ) ? 6 : 8)
+// PRE: every term carries its own factor and sign:  c*((k0*d_x +/- k1*d_y) +/- k2*d_z)
+template <typename T, int R, bool HY, int VY, int VZ, int SCALE, bool BZ, bool PRE>
+__global__ void __launch_bounds__(128, (SCALE == 3 || BZ || PRE) ? 6 : 8)
 star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   constexpr int VN = Vec<T>::N;
   constexpr int NP = 2 * R + 1;
@@ -143,7 +144,16 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
               }
               dy = lean_scale<T, SCALE>(dy, ay);
               saw_inf |= is_inf(dy);
-              total = add_rn(add_rn(dx, dy), dz);
+              if (PRE) {
+                const T a = mul_rn(dx, P.pre[0]), b = mul_rn(dy, P.pre[1]), cz = mul_rn(dz, P.pre[2]);
+                const T ab = P.subtract[1] ? sub_rn(a, b) : add_rn(a, b);
+                total = P.subtract[2] ? sub_rn(ab, cz) : add_rn(ab, cz);
+              } else {
+                total = add_rn(add_rn(dx, dy), dz);
+              }
+            } else if (PRE) {
+              const T a = mul_rn(dx, P.pre[0]), cz = mul_rn(dz, P.pre[1]);
+              total = P.subtract[1] ? sub_rn(a, cz) : add_rn(a, cz);
             } else {
               total = add_rn(dx, dz);
             }
@@ -183,11 +193,17 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
 
 template <typename T, int R, bool HY, int VY, int VZ>
 static void launch_lean(StarParams<T>& P, dim3 grid, dim3 block, bool bz, cudaStream_t stream) {
-#define FD_LEAN(SC)                                                                 \
-  if (bz)                                                                           \
-    star_lean_kernel<T, R, HY, VY, VZ, SC, true><<<grid, block, 0, stream>>>(P);    \
-  else                                                                              \
-    star_lean_kernel<T, R, HY, VY, VZ, SC, false><<<grid, block, 0, stream>>>(P);
+#define FD_LEAN(SC)                                                                        \
+  if (P.lean_expr == 2) {                                                                  \
+    if (bz)                                                                                \
+      star_lean_kernel<T, R, HY, VY, VZ, SC, true, true><<<grid, block, 0, stream>>>(P);   \
+    else                                                                                   \
+      star_lean_kernel<T, R, HY, VY, VZ, SC, false, true><<<grid, block, 0, stream>>>(P);  \
+  } else if (bz) {                                                                         \
+    star_lean_kernel<T, R, HY, VY, VZ, SC, true, false><<<grid, block, 0, stream>>>(P);    \
+  } else {                                                                                 \
+    star_lean_kernel<T, R, HY, VY, VZ, SC, false, false><<<grid, block, 0, stream>>>(P);   \
+  }
   if (P.scale_class == 0) {
     FD_LEAN(0)
   } else if (P.scale_class == 1) {
@@ -206,8 +222,10 @@ bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
     return false;
   } else {
     const DevFused<T>& F = P.F;
-    const bool bz = mode == 1 && P.only_z_bounded;          // clean in x and y, fixed along z
-    if (!(mode == 0 || bz) || F.depth != 1 || !P.prev_is_src[0] || F.dot_out || (axes != 3 && axes != 4)) return false;
+    (void)mode;
+    const bool bz = !P.clean && P.only_z_bounded;           // clean in x and y, fixed along z
+    if (!P.lean_expr || !(P.clean || bz) || F.depth != 1 || !P.prev_is_src[0] || F.dot_out || (axes != 3 && axes != 4))
+      return false;
     if (P.scale_class == 2) return false;                      // IEEE division somewhere: general kernel
     const int rows = F.box_hi[1] - F.box_lo[1], vecs = (F.box_hi[2] - F.box_lo[2]) / VN, nx = F.box_hi[0] - F.box_lo[0];
     if (rows <= 0 || vecs <= 0 || nx <= 0) return false;

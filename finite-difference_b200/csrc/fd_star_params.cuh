@@ -41,6 +41,8 @@ struct StarParams {
   int32_t subtract[3], negate[3], has_pre[3];
   T pre[3];
   int32_t nterms, x_chunk, has_mul;
+  int32_t clean;            // no output of the box is outside a term's [lo, hi), no face touches it
+  int32_t lean_expr;        // 0: not a lean expression; 1: c*(sum of ders in axis order); 2: same with per-term factors / minus signs
   int32_t only_z_bounded;   // the box is clean along x and y; only the contiguous axis has a rim in it
   int32_t scale_class;   // 0: every axis divides by 1; 1: exact reciprocal multiplies; 3: FMA-corrected; 2: IEEE division somewhere
   int32_t prev_is_src[2];
@@ -114,7 +116,7 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
   P->src = t0.src;
   P->nterms = F.nterms;
   const int naxes = F.nterms;
-  bool canonical = true;
+  bool canonical = true, ordered = true;   // ordered: terms follow the axes, none negated
   int scale_class = 0;
   for (int k = 0; k < 3; ++k) {
     P->order[k] = 2;
@@ -148,6 +150,8 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
     P->has_pre[k] = t.has_pre;
     P->pre[k] = t.pre;
     if (t.axis != canon[axes_code][k] || t.negate || t.has_pre || (k > 0 && t.subtract)) canonical = false;
+    if (t.axis != canon[axes_code][k] || t.negate) ordered = false;
+    if (!t.has_pre) P->pre[k] = (T)1;        // multiplying by 1 is exact
   }
   P->has_mul = 0;
   P->mul = (T)1;
@@ -181,6 +185,8 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
     }
   P->only_z_bounded = (!clean && clean_xy) ? 1 : 0;
   P->scale_class = scale_class;
+  P->clean = clean ? 1 : 0;
+  P->lean_expr = !simple_post ? 0 : (canonical ? 1 : (ordered ? 2 : 0));
   *mode = (canonical && simple_post) ? (clean ? 0 : 1) : 2;
   return true;
 }
