@@ -218,10 +218,10 @@ class Engine:
 
     def wants_level(self, t):
         h = self.model.history
+        if h == "last":
+            return False          # fetched on demand (Field.data / data_level), nothing streamed
         if t == self.n_t - 1 or h == "all":
             return True
-        if h == "last":
-            return False
         return t % h == 0
 
     # --------------------------------------------------------------- execute
@@ -781,6 +781,18 @@ class Engine:
         self.pending_copies.append((st, k, t, host, done))
         if len(self.pending_copies) > 64:
             self.drain_copies(keep=32)
+
+    def fetch_into(self, field, t, out):
+        """Level ``t`` of ``field`` from its ring slot into the caller's host array."""
+        st = self.states.get(id(field))
+        if st is None or st.constant or st.held[st.slot_index(t)] != t:
+            return False
+        if out.shape != tuple(field._slice_shape) or out.dtype != self.dtype or not out.flags.c_contiguous:
+            return False
+        import torch
+        torch.from_numpy(out.reshape(-1)).copy_(st.owned(st.ring[st.slot_index(t)]))
+        self.poll(final=True)
+        return True
 
     def wait_for_copies(self, st, slot):
         """The compute stream must not overwrite a ring slot that is still being

@@ -5,7 +5,8 @@ Additive options (defaults reproduce the reference):
   dtype     np.float64 (reference) or np.float32
   history   "all" (reference: every level of every field comes back to
             ``Field.data``), an integer K (every K-th level plus the last
-            one), or "last" (only the level the model currently stands on)
+            one), or "last" (nothing is streamed; ``Field.data`` fetches the level
+            the model currently stands on; ``.dot`` levels are not kept)
 """
 
 from __future__ import annotations

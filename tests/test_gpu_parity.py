@@ -301,3 +301,14 @@ def test_invariant_division_is_correctly_rounded(dtype):
             with np.errstate(all="ignore"):
                 want = vals / dtype(scale)
             assert np.array_equal(outs[0], want, equal_nan=True), scale
+
+
+def test_local_level_into_caller_buffer(fd):
+    shape = (16, 20, 24)
+    ic = np.random.default_rng(51).random(shape)
+    m, T = _heat(fd, shape, 5, True, 0.1, 1e-3, ic, history="last")
+    want, _ = O.run_heat(shape, 5, True, 0.1, 1e-3, ic)
+    out = np.empty(shape)
+    got = T.local_level(4, out=out)
+    assert got is out and np.array_equal(out, want[4])
+    assert np.array_equal(T.local_level(4), want[4])
