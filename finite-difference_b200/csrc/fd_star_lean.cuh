@@ -28,7 +28,7 @@ __device__ __forceinline__ T lean_scale(T v, const StarAxis<T>& a) {
 // peeled off as a thin slab without giving up whole 128-bit vector groups).
 // PRE: every term carries its own factor and sign:  c*((k0*d_x +/- k1*d_y) +/- k2*d_z)
 template <typename T, int R, bool HY, int VY, int VZ, int SCALE, bool BZ, bool PRE>
-__global__ void __launch_bounds__(128, (SCALE == 3 || BZ || PRE) ? 6 : 8)
+__global__ void __launch_bounds__(128, R > 1 ? 4 : ((SCALE == 3 || BZ || PRE) ? 6 : 8))
 star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   constexpr int VN = Vec<T>::N;
   constexpr int NP = 2 * R + 1;
@@ -218,7 +218,7 @@ static void launch_lean(StarParams<T>& P, dim3 grid, dim3 block, bool bz, cudaSt
 template <typename T, int R>
 bool try_star_lean(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
   constexpr int VN = Vec<T>::N;
-  if constexpr (R != 1) {     // wider stencils spill at the 64 registers this kernel is tuned for
+  if constexpr (R > VN || R > 2) {   // z neighbours come from one vector per side; radius 3, 4: general kernel
     return false;
   } else {
     const DevFused<T>& F = P.F;
