@@ -66,6 +66,8 @@ class FieldState:
         self.counts_checked = engine.model.time_step
         s = len(field._slice_shape)
         self.dims3 = (1,) * (3 - s) + tuple(self.ext_shape) if s <= 3 else None
+        if not self.constant:
+            self._discover_array_faces()
         if self.constant:
             self.load_level(0)
         elif self.integrated:
@@ -73,6 +75,40 @@ class FieldState:
 
     def slot_index(self, t):
         return t % len(self.ring)
+
+    def _discover_array_faces(self):
+        """Boundary values written straight into ``Field.data`` (set_BC only takes
+        strings, so array-valued boundaries are written into the future time levels
+        by hand, exactly like array initial conditions): any boundary face of a
+        fixed axis that holds known values at a future level is treated like a
+        set_BC face.  Known future values anywhere else cannot be honoured."""
+        f, model = self.field, self.engine.model
+        dense = f._hist.dense
+        t_from = model.time_step + 1
+        if dense is None or t_from >= self.engine.n_t:
+            return
+        t_pos = model._names.index(model.time_axis)
+        future = np.moveaxis(dense, t_pos, 0)[t_from:]
+        known = ~np.isnan(future)
+        if not known.any():
+            return
+        space = [a for a in model._names if a != model.time_axis]
+        for k, axis in enumerate(space):
+            if axis in model.periodic:
+                continue
+            for idx in (0, -1):
+                sel = [slice(None)] * future.ndim
+                sel[1 + k] = idx
+                if known[tuple(sel)].any() and (axis, idx) not in f._bc_locations:
+                    f._bc_locations.append((axis, idx))
+        for axis, idx in f._bc_locations:
+            sel = [slice(None)] * future.ndim
+            sel[1 + space.index(axis)] = idx
+            known[tuple(sel)] = False
+        if known.any():
+            raise NotImplementedError(
+                f"field {f.name}: values were written into future time levels of Field.data away from the "
+                "boundary faces; the B200 engine only pre-populates boundary faces")
 
     def load_level(self, t):
         """Host history -> device (initial condition, constant coefficient)."""

@@ -81,6 +81,29 @@ def heat2d_fixed(fd, nx=12, ny=10, n_t=6, k=0.1, dt=1e-3, seed=0):
     return {"T": T.data, "Tdot": T.dot.data}
 
 
+def heat2d_array_bc(fd, nx=10, ny=9, n_t=5, seed=16):
+    """Boundary values written into Field.data by hand for every time level (the
+    array counterpart of set_BC, which only takes strings)."""
+    m = fd.Model({"t": np.arange(n_t) * 1e-3, "x": np.arange(nx) * 1.0, "y": np.arange(ny) * 1.0}, "t")
+    T = fd.Field(m, "T", n_time_ders=1)
+    d2 = fd.Stencil([-1, 0, 1], 2)
+    rng = _rng(seed)
+    data = T.data
+    data[0] = rng.random((nx, ny))
+    data[:, 0, :] = rng.random((n_t, ny))
+    data[:, -1, :] = 2.0
+    data[:, :, 0] = rng.random((n_t, nx))
+    data[:, :, -1] = np.arange(n_t)[:, None] * 0.5
+    T.IC_set = True
+
+    def body():
+        T.dot.assign_update(0.1 * (d2.der(T.prev, "x") + d2.der(T.prev, "y")))
+        T.time_integrate_update()
+
+    _loop(m, body)
+    return {"T": T.data, "Tdot": T.dot.data}
+
+
 # -- C.3 ---------------------------------------------------------------------
 
 def heat3d_periodic(fd, shape=(6, 5, 4), n_t=7, k=0.1, dt=1e-3, seed=0):
@@ -383,6 +406,7 @@ def bc_conflict_prints(fd):
 ALL = {
     "readme_1d": readme_1d,
     "heat2d_fixed": heat2d_fixed,
+    "heat2d_array_bc": heat2d_array_bc,
     "heat3d_periodic": heat3d_periodic,
     "heat3d_fixed": heat3d_fixed,
     "heat1d_odd_dx": heat1d_odd_dx,
