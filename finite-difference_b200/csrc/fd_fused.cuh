@@ -92,9 +92,10 @@ struct DevFused {
 };
 
 template <typename T>
-inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P) {
+inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P, int min_terms = 1) {
   if (!d) return fail("fd_fused_step: descriptor is NULL");
-  if (d->nterms < 1 || d->nterms > FD_MAX_TERMS)
+  memset((void*)&P->term[0], 0, sizeof(P->term[0]));
+  if (d->nterms < min_terms || d->nterms > FD_MAX_TERMS)
     return fail("fd_fused_step: %d terms, supported 1..%d", d->nterms, FD_MAX_TERMS);
   if (d->npost < 0 || d->npost > FD_MAX_POST)
     return fail("fd_fused_step: %d post operations, supported 0..%d", d->npost, FD_MAX_POST);

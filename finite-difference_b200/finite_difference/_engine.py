@@ -227,6 +227,7 @@ class Engine:
         self.split_rim = os.environ.get("FD_B200_NO_SPLIT", "0") != "1"
         self.overlap = os.environ.get("FD_B200_NO_OVERLAP", "0") != "1"
         self.fuse_pairs = os.environ.get("FD_B200_NO_PAIR", "0") != "1"
+        self.fuse_expr = os.environ.get("FD_B200_NO_EXPR", "0") != "1"
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
         default_poll = 16 if points < (1 << 20) else 64
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
@@ -237,7 +238,7 @@ class Engine:
         self.stats = {"fused": 0, "unfused_statements": 0}
         self._fn = {name: nat.fn(name, self.dtype) for name in
                     ("fd_der", "fd_ewise", "fd_merge_store", "fd_fill", "fd_face_store", "fd_count_nan",
-                     "fd_fused_step", "fd_fused_pair")}
+                     "fd_fused_step", "fd_fused_pair", "fd_fused_expr")}
 
     # ------------------------------------------------------------------ utils
     def state(self, field):
@@ -321,11 +322,16 @@ class Engine:
         if dims3 is None or dot_field._bc_locations:
             return None
         matched = _match_statement(node)
-        if matched is None:
-            return None
-        terms, posts = matched
-        if len(terms) > nat.FD_MAX_TERMS or len(posts) > nat.FD_MAX_POST:
-            return None
+        program = None
+        if matched is None or len(matched[0]) > nat.FD_MAX_TERMS or len(matched[1]) > nat.FD_MAX_POST:
+            # not a sum of der terms: a general point-wise expression, evaluated
+            # per point by the postfix-program kernel (fd_fused_expr)
+            program = _compile_expr(node) if self.fuse_expr else None
+            if program is None:
+                return None
+            terms, posts = [(der, False, None, False) for der in program[0]], []
+        else:
+            terms, posts = matched
         levels = [self.state(p) for _, p in chain]
         if any(ls.field._slice_shape != dot_field._slice_shape for ls in levels):
             return None
@@ -333,13 +339,29 @@ class Engine:
             return None
         pad = 3 - len(dot_field._slice_shape)
 
-        d = nat.Fused()
+        top = nat.Expr() if program is not None else None
+        d = top.base if top is not None else nat.Fused()
         sources = []
         for a in range(3):
             d.n[a] = dims3[a]
         d.nterms = len(terms)
+        if program is not None:
+            _, leaves, code = program
+            top.nfields, top.ncode = len(leaves), len(code)
+            for j, leaf in enumerate(leaves):
+                if leaf.shape != tuple(dot_field._slice_shape):
+                    return None
+                try:
+                    top.field[j] = self.state(leaf.field).level(leaf.t).data_ptr()
+                except RuntimeError:
+                    return None
+                sources.append((self.state(leaf.field), leaf.t - t, False))
+            for pc, (op, arg, imm) in enumerate(code):
+                top.op[pc], top.arg[pc], top.imm[pc] = op, arg, imm
         for k, (der, subtract, pre, negate) in enumerate(terms):
             leaf = der.a
+            if der.shape != tuple(dot_field._slice_shape):
+                return None
             src_state = self.state(leaf.field)
             try:
                 src = src_state.level(leaf.t)
@@ -391,7 +413,7 @@ class Engine:
             d.rim_lo[a], d.rim_hi[a] = 0, max(dims3[a] - 1, 0)
         if self.H:
             d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
-        return d, dot_state, levels, sources, dyn_faces, pad, dims3
+        return d, dot_state, levels, sources, dyn_faces, pad, dims3, top
 
     def _try_fused(self, dot_field, node, chain, t, reads_new):
         # the same statement comes back every step: its launch descriptor is
@@ -406,7 +428,7 @@ class Engine:
                 self._plans.clear()
                 self._box_cache.clear()
             self._plans[key] = plan
-        d, dot_state, levels, sources, dyn_faces, pad, dims3 = plan
+        d, dot_state, levels, sources, dyn_faces, pad, dims3, top = plan
         for src_state, offset, slab in sources:
             try:
                 src_state.level(t + offset)
@@ -430,13 +452,17 @@ class Engine:
             # only the owned planes are computed; the domain faces of the slab
             # axis sit on the first / last owned plane of the end ranks
             region[pad] = [self.H, self.H + dot_state.owned0]
-        launch = self._fn["fd_fused_step"]
+        launch = self._fn["fd_fused_step" if top is None else "fd_fused_expr"]
+        ref = C.byref(d if top is None else top)
+        if top is not None:
+            self.stats["fused_expr"] = self.stats.get("fused_expr", 0) + 1
 
         def run(piece):
             bkey = (id(d), tuple(map(tuple, piece)))
             boxes = self._box_cache.get(bkey)
             if boxes is None:
-                boxes = self._box_cache[bkey] = self._split_boxes(d, piece)
+                # (the expression kernel has a single instantiation: nothing to gain from an interior box)
+                boxes = self._box_cache[bkey] = self._split_boxes(d, piece) if top is None else [piece]
             rim_stream = self.dev.rim_stream if len(boxes) > 1 else None
             if rim_stream is not None:
                 # the rim slabs read the same level and write disjoint points:
@@ -448,7 +474,7 @@ class Engine:
                 for a in range(3):
                     d.box_lo[a], d.box_hi[a] = box[a]
                 stream = rim_stream.cuda_stream if (i and rim_stream is not None) else self.stream
-                nat.check(launch(C.byref(d), stream))
+                nat.check(launch(ref, stream))
             if rim_stream is not None:
                 done = self.dev.event()
                 done.record(rim_stream)
@@ -909,6 +935,74 @@ class Engine:
                     print(LOSING_MSG)
                     self.model.insufficient_bc = True
                     return
+
+
+_X_BIN = {"add": nat.X_ADD, "sub": nat.X_SUB, "mul": nat.X_MUL, "truediv": nat.X_DIV, "pow": nat.X_POW}
+_X_IMM = {"add": nat.X_ADD_IMM, "sub": nat.X_SUB_IMM, "mul": nat.X_MUL_IMM, "truediv": nat.X_DIV_IMM}
+_X_POW = {2.0: nat.X_SQUARE, 0.5: nat.X_SQRT, -1.0: nat.X_RECIP}   # numpy's scalar-exponent fast paths
+
+
+def _compile_expr(node):
+    """Expression tree -> postfix program for fd_fused_expr: (der nodes, field
+    leaves, [(op, arg, imm)]), or None if it does not fit the kernel's limits
+    (der of an intermediate expression, too many operands, too deep)."""
+    ders, leaves, code = [], [], []
+    depth = [0, 0]
+
+    def push(n=1):
+        depth[0] += n
+        depth[1] = max(depth[1], depth[0])
+
+    def emit(n):
+        if isinstance(n, Der):
+            if not isinstance(n.a, Leaf):
+                raise ValueError
+            key = n.key()
+            for k, other in enumerate(ders):
+                if other is n or other.key() == key:
+                    break
+            else:
+                ders.append(n)
+                k = len(ders) - 1
+            code.append((nat.X_PUSH_DER, k, 0.0))
+            push()
+        elif isinstance(n, Leaf):
+            for k, other in enumerate(leaves):
+                if other.field is n.field and other.t == n.t:
+                    break
+            else:
+                leaves.append(n)
+                k = len(leaves) - 1
+            code.append((nat.X_PUSH_FIELD, k, 0.0))
+            push()
+        elif isinstance(n, Unary):
+            emit(n.a)
+            code.append((nat.X_NEG, 0, 0.0))
+        elif isinstance(n, Binary) and isinstance(n.a, Node) and isinstance(n.b, Node):
+            emit(n.a)
+            emit(n.b)
+            code.append((_X_BIN[n.op], 0, 0.0))
+            push(-1)
+        elif isinstance(n, Binary) and isinstance(n.a, Node):
+            emit(n.a)
+            s = float(n.b)
+            if n.op == "pow":
+                if s == 1.0:
+                    return
+                code.append((_X_POW.get(s, nat.X_POW_IMM), 0, s))
+            else:
+                code.append((_X_IMM[n.op], 0, s))
+        else:
+            raise ValueError
+
+    try:
+        emit(node)
+    except (ValueError, KeyError):
+        return None
+    if (len(ders) > nat.FD_MAX_TERMS or len(leaves) > nat.FD_EXPR_MAX_FIELDS or not code
+            or len(code) > nat.FD_EXPR_MAX_CODE or depth[1] > nat.FD_EXPR_MAX_STACK):
+        return None
+    return ders, leaves, code
 
 
 def _slab_reach(stmts):

@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 FD_MAX_POINTS = 16
 FD_MAX_TERMS = 4
 FD_MAX_POST = 4
@@ -83,6 +83,21 @@ class Pair(C.Structure):
                 ("box_lo", C.c_int32 * 3), ("box_hi", C.c_int32 * 3)]
 
 
+FD_EXPR_MAX_FIELDS, FD_EXPR_MAX_CODE, FD_EXPR_MAX_STACK = 4, 32, 8
+# enum fd_expr_op
+(X_PUSH_DER, X_PUSH_FIELD, X_PUSH_IMM, X_NEG, X_ADD, X_SUB, X_MUL, X_DIV, X_POW, X_ADD_IMM, X_SUB_IMM, X_MUL_IMM,
+ X_DIV_IMM, X_POW_IMM, X_SQUARE, X_RECIP, X_SQRT) = range(17)
+
+
+class Expr(C.Structure):
+    _fields_ = [("base", Fused),
+                ("nfields", C.c_int32), ("ncode", C.c_int32),
+                ("field", C.c_void_p * FD_EXPR_MAX_FIELDS),
+                ("op", C.c_int32 * FD_EXPR_MAX_CODE),
+                ("arg", C.c_int32 * FD_EXPR_MAX_CODE),
+                ("imm", C.c_double * FD_EXPR_MAX_CODE)]
+
+
 _I64, _P, _D, _I = C.c_int64, C.c_void_p, C.c_double, C.c_int
 
 # name -> (restype, argtypes); every symbol include/fd_b200.h declares
@@ -101,6 +116,7 @@ for _sfx in ("f64", "f32"):
         f"fd_count_nan_{_sfx}": (_I, [_P, _I64, _P, _P]),
         f"fd_fused_step_{_sfx}": (_I, [C.POINTER(Fused), _P]),
         f"fd_fused_pair_{_sfx}": (_I, [C.POINTER(Pair), _P]),
+        f"fd_fused_expr_{_sfx}": (_I, [C.POINTER(Expr), _P]),
     })
 
 

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define FD_ABI_VERSION 3
+#define FD_ABI_VERSION 4
 
 #define FD_MAX_POINTS 16 /* sample points per stencil                     */
 #define FD_MAX_TERMS 4   /* der() terms summed by one fused statement     */
@@ -255,6 +255,43 @@ typedef struct fd_pair {
 
 int fd_fused_pair_f64(const fd_pair_t* desc, void* stream);
 int fd_fused_pair_f32(const fd_pair_t* desc, void* stream);
+
+/* ---- fused statement with a general point-wise expression ----------------- */
+
+/* Any FieldInstant expression (FD.py:794-869) over der terms (FD.py:990-1122),
+ * stored field levels and numbers -- products of fields, powers, quotients --
+ * followed by the same assign_update / time_integrate_update chain as
+ * fd_fused_step, in one pass.  The expression is a postfix program evaluated
+ * per point on a small value stack; every operation is the same IEEE operation
+ * the unfused fd_ewise kernels perform, in the same order. */
+#define FD_EXPR_MAX_FIELDS 4
+#define FD_EXPR_MAX_CODE 32
+#define FD_EXPR_MAX_STACK 8
+
+enum fd_expr_op {
+  FD_X_PUSH_DER = 0, /* arg: index into base.term                     */
+  FD_X_PUSH_FIELD,   /* arg: index into field[]                       */
+  FD_X_PUSH_IMM,     /* imm                                           */
+  FD_X_NEG,          /* top = -top                                    */
+  FD_X_ADD, FD_X_SUB, FD_X_MUL, FD_X_DIV, FD_X_POW,             /* b = pop, a = pop, push a op b */
+  FD_X_ADD_IMM, FD_X_SUB_IMM, FD_X_MUL_IMM, FD_X_DIV_IMM, FD_X_POW_IMM, /* top = top op imm */
+  FD_X_SQUARE, FD_X_RECIP, FD_X_SQRT                             /* numpy's scalar-power fast paths */
+};
+
+typedef struct fd_expr {
+  fd_fused_t base;   /* extents, der terms (subtract/pre/negate and post are not
+                        used: nterms may be 0, npost must be 0), Euler chain,
+                        faces, counters, box */
+  int32_t nfields;
+  int32_t ncode;
+  const void* field[FD_EXPR_MAX_FIELDS]; /* levels with the target's dimensions */
+  int32_t op[FD_EXPR_MAX_CODE];
+  int32_t arg[FD_EXPR_MAX_CODE];
+  double imm[FD_EXPR_MAX_CODE];
+} fd_expr_t;
+
+int fd_fused_expr_f64(const fd_expr_t* desc, void* stream);
+int fd_fused_expr_f32(const fd_expr_t* desc, void* stream);
 
 #ifdef __cplusplus
 }

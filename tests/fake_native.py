@@ -40,7 +40,7 @@ class FakeLib:
         self.error = b""
 
     def fd_abi_version(self):
-        return 3
+        return 4
 
     def fd_last_error(self):
         return self.error
@@ -235,6 +235,82 @@ def _pair(self, desc, stream):
 
 
 FakeLib.fd_fused_pair_f64 = _pair
+
+
+def _expr(self, desc, stream):
+    """fd_fused_expr_f64 in numpy: run the postfix program on whole arrays, then
+    reuse the fused step's epilogue through a one-term trick-free path."""
+    self.launches += 1
+    x = desc._obj if hasattr(desc, "_obj") else desc.contents
+    d = x.base
+    n = tuple(d.n)
+    size = int(np.prod(n))
+    flags = _arr(d.flags, 4, np.int64) if d.flags else None
+    stack = []
+    with np.errstate(all="ignore"):
+        for pc in range(x.ncode):
+            op, arg, imm = x.op[pc], x.arg[pc], x.imm[pc]
+            if op == 0:
+                tm = d.term[arg]
+                shifts, weights, scale = self._stencil(tm.st)
+                sshape = list(n)
+                sshape[tm.axis] = tm.n_src
+                src = _arr(tm.src, int(np.prod(sshape))).reshape(sshape)
+                stack.append(self._der(src, tm.axis, shifts, weights, scale, tm.periodic, tm.lo, tm.hi, n[tm.axis], flags))
+            elif op == 1:
+                stack.append(np.array(_arr(x.field[arg], size).reshape(n)))
+            elif op == 2:
+                stack.append(np.full(n, imm))
+            elif op == 3:
+                stack[-1] = -stack[-1]
+            elif 4 <= op <= 8:
+                b = stack.pop()
+                a = stack.pop()
+                stack.append([a + b, a - b, a * b, a / b, a ** b][op - 4] if False else
+                             (a + b if op == 4 else a - b if op == 5 else a * b if op == 6 else a / b if op == 7 else a ** b))
+            elif 9 <= op <= 13:
+                a = stack[-1]
+                stack[-1] = (a + imm if op == 9 else a - imm if op == 10 else a * imm if op == 11 else
+                             a / imm if op == 12 else a ** imm)
+            elif op == 14:
+                stack[-1] = stack[-1] * stack[-1]
+            elif op == 15:
+                stack[-1] = 1 / stack[-1]
+            elif op == 16:
+                stack[-1] = np.sqrt(stack[-1])
+    assert len(stack) == 1
+    total = stack[0]
+    region = tuple(slice(d.box_lo[a], d.box_hi[a]) for a in range(3)) if any(d.box_hi) else (slice(None),) * 3
+    if d.dot_out:
+        _arr(d.dot_out, size).reshape(n)[region] = total[region]
+    rate = total
+    for l in range(d.depth):
+        new = _arr(d.prev[l], size).reshape(n) + rate * d.dt
+        stored = np.full(n, np.nan)
+        for dim in range(3):
+            for side in range(2):
+                fp = d.face[l][dim][side]
+                if not fp:
+                    continue
+                fshape = [n[a] for a in range(3) if a != dim]
+                face = _arr(fp, int(np.prod(fshape))).reshape(fshape)
+                sel = [slice(None)] * 3
+                sel[dim] = d.rim_lo[dim] if side == 0 else d.rim_hi[dim]
+                tgt = stored[tuple(sel)]
+                fill = np.isnan(tgt)
+                tgt[fill] = face[fill]
+        known = ~np.isnan(new)
+        if flags is not None and np.any(~np.isnan(stored[region][known[region]])):
+            flags[1] = 1
+        new[~known] = stored[~known]
+        _arr(d.out[l], size).reshape(n)[region] = new[region]
+        if d.nan_count[l]:
+            _arr(d.nan_count[l], 1, np.int64)[0] += int(np.isnan(new[region]).sum())
+        rate = new
+    return 0
+
+
+FakeLib.fd_fused_expr_f64 = _expr
 
 
 class FakeDevice:

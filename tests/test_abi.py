@@ -31,7 +31,7 @@ def test_struct_sizes_match_the_header():
     import subprocess
     import tempfile
     import finite_difference._native as nat
-    src = '#include <stdio.h>\n#include "fd_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(fd_stencil_t), sizeof(fd_term_t), sizeof(fd_post_t), sizeof(fd_fused_t), sizeof(fd_pair_axis_t), sizeof(fd_pair_t));return 0;}\n'
+    src = '#include <stdio.h>\n#include "fd_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(fd_stencil_t), sizeof(fd_term_t), sizeof(fd_post_t), sizeof(fd_fused_t), sizeof(fd_pair_axis_t), sizeof(fd_pair_t), sizeof(fd_expr_t));return 0;}\n'
     with tempfile.TemporaryDirectory() as tmp:
         c = os.path.join(tmp, "s.c")
         open(c, "w").write(src)
@@ -39,7 +39,7 @@ def test_struct_sizes_match_the_header():
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
         sizes = [int(v) for v in subprocess.check_output([exe]).split()]
     assert sizes == [ctypes.sizeof(nat.Stencil), ctypes.sizeof(nat.Term), ctypes.sizeof(nat.Post),
-                     ctypes.sizeof(nat.Fused), ctypes.sizeof(nat.PairAxis), ctypes.sizeof(nat.Pair)]
+                     ctypes.sizeof(nat.Fused), ctypes.sizeof(nat.PairAxis), ctypes.sizeof(nat.Pair), ctypes.sizeof(nat.Expr)]
 
 
 def test_missing_device_fails_loudly():

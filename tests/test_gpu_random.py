@@ -117,3 +117,49 @@ def test_fused_equals_unfused_on_random_models(block):
         for g, w in zip(got, want):
             assert np.array_equal(g, w, equal_nan=True), (spec, stats)
     assert n_fused >= len(specs) // 2
+
+
+def _gray_scott(fd, shape, fuse, dtype=np.float64, steps=5):
+    """Two coupled reaction-diffusion fields: products and powers of fields next
+    to der terms (general point-wise expression kernel)."""
+    os.environ["FD_B200_NO_FUSE"] = "0" if fuse else "1"
+    try:
+        rng = np.random.default_rng(7)
+        names = ["x", "y", "z"][:len(shape)]
+        axes = {"t": np.arange(steps + 1) * 0.05}
+        for n, a in zip(shape, names):
+            axes[a] = np.arange(n) * 0.5
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model(axes, "t", periodic=tuple(names), dtype=dtype)
+            u = fd.Field(m, "u", n_time_ders=1)
+            v = fd.Field(m, "v", n_time_ders=1)
+            d2 = fd.Stencil([-1, 0, 1], 2)
+            d1 = fd.Stencil([-1, 0, 1], 1)
+            u.set_IC_values((0.5 + 0.5 * rng.random(shape)).astype(dtype))
+            v.set_IC_values((0.25 * rng.random(shape)).astype(dtype))
+            while not m.finished:
+                lap_u = d2.der(u.prev, names[0])
+                lap_v = d2.der(v.prev, names[0])
+                for a in names[1:]:
+                    lap_u = lap_u + d2.der(u.prev, a)
+                    lap_v = lap_v + d2.der(v.prev, a)
+                uvv = u.prev * v.prev ** 2
+                u.dot.assign_update(0.16 * lap_u - uvv + 0.035 * (1 - u.prev) - u.prev * d1.der(u.prev, names[-1]) / 7)
+                v.dot.assign_update(0.08 * lap_v + uvv - (0.035 + 0.065) * v.prev + (v.prev ** 0.5) * 1e-3)
+                u.time_integrate_update()
+                v.time_integrate_update()
+                m.increment_time()
+            return np.array(u.data), np.array(v.data), dict(m._engine.stats)
+    finally:
+        os.environ.pop("FD_B200_NO_FUSE", None)
+
+
+@pytest.mark.parametrize("shape", [(300,), (65, 130), (20, 24, 70)])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_expression_kernel_equals_unfused(shape, dtype):
+    import finite_difference as fd
+    u1, v1, st1 = _gray_scott(fd, shape, True, dtype)
+    u0, v0, st0 = _gray_scott(fd, shape, False, dtype)
+    assert st1.get("fused_expr", 0) == 10 and st1["unfused_statements"] == 0, st1
+    assert st0["fused"] == 0
+    assert np.array_equal(u1, u0, equal_nan=True) and np.array_equal(v1, v0, equal_nan=True)
