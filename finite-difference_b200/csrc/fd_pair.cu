@@ -165,6 +165,12 @@ pair_kernel(const __grid_constant__ PairParams<T> P) {
   for (int a = 0; a < NA; ++a) warp_add_count(P.ax[a].v_nan, nan_v[a]);
 }
 
+}  // namespace fdb
+
+#include "fd_pair_march.cuh"
+
+namespace fdb {
+
 template <typename T>
 static int pair_impl(const fd_pair_t* d, void* stream) {
   constexpr int VN = Vec<T>::N;
@@ -243,6 +249,11 @@ static int pair_impl(const fd_pair_t* d, void* stream) {
     // mode 0 under class 1: multiplying by inv == 1 is exact
   }
   cudaStream_t st = (cudaStream_t)stream;
+  {
+    bool any_dot = d->pdot_out != nullptr;
+    for (int a = 0; a < d->naxes; ++a) any_dot |= d->ax[a].vdot_out != nullptr;
+    if (try_pair_march<T>(P, d->naxes, any_dot, scale_class, st)) return check_launch("fd_fused_pair(march)");
+  }
 #define FD_PAIR(NA)                                                        \
   if (scale_class == 0)                                                    \
     pair_kernel<T, NA, 0><<<grid, block, 0, st>>>(P);                      \

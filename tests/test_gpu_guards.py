@@ -82,10 +82,13 @@ def test_heat_with_guard_zones(shape, periodic, points):
     assert np.array_equal(got, want[3], equal_nan=True)
 
 
+@pytest.mark.parametrize("march", [False, True])
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
-def test_staggered_pair_with_guard_zones(dtype):
+def test_staggered_pair_with_guard_zones(dtype, march, monkeypatch):
     import finite_difference as fd
     from tests.test_gpu_parity import _acoustic
+    if march:   # a forced chunk length also forces the marching kernel on this small grid
+        monkeypatch.setenv("FD_B200_PAIR_CHUNK", "4")
     shape, n_t = (10, 12, 40), 5
     ic = np.random.default_rng(62).random(shape).astype(dtype)
     with guarded_allocations() as bases:

@@ -236,6 +236,54 @@ def test_fp64_staggered_pair_kernel(fd):
     assert m._engine.stats.get("fused_pairs") == n_t - 1
 
 
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("variant", ["default", "march_vy1", "march_vy2", "no_march"])
+def test_staggered_marching_pair_kernel(fd, monkeypatch, dtype, variant):
+    """The marching pair kernel (large periodic 3-D staggered models; csrc/fd_pair_march.cuh),
+    the plain pair kernel and the oracle agree bit for bit; the grid is large
+    enough for the library to pick the marching kernel on its own."""
+    if variant == "no_march":
+        monkeypatch.setenv("FD_B200_NO_MARCH", "1")
+    elif variant != "default":
+        monkeypatch.setenv("FD_B200_PAIR_CHUNK", "8")
+        monkeypatch.setenv("FD_B200_PAIR_VY", variant[-1])
+    shape, n_t = (64, 128, 512), 4
+    ic = np.random.default_rng(35).random(shape).astype(dtype)
+    m, p, v = _acoustic(fd, shape, n_t, True, ic, dtype)
+    want, want_v = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic, dtype=dtype)
+    assert np.array_equal(p.data, want.astype(np.float64), equal_nan=True)
+    for a, w in zip("xyz", want_v):
+        assert np.array_equal(v[a].data, w.astype(np.float64), equal_nan=True)
+    assert m._engine.stats.get("fused_pairs") == n_t - 1
+
+
+def test_marching_pair_kernel_reports_nan_and_inf(fd, monkeypatch):
+    """NaN counts and the infinite-der flag of the marching kernel come from its
+    two-stage test (finite magnitude sum, else exact): same deferred messages
+    as the plain pair kernel."""
+    import contextlib, io
+    outcomes = []
+    for march in (True, False):
+        if march:
+            monkeypatch.setenv("FD_B200_PAIR_CHUNK", "8")
+        else:
+            monkeypatch.delenv("FD_B200_PAIR_CHUNK")
+            monkeypatch.setenv("FD_B200_NO_MARCH", "1")
+        shape, n_t = (12, 16, 64), 4
+        ic = np.random.default_rng(36).random(shape)
+        ic[3, 4, 5] = np.inf
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            try:
+                m, p, v = _acoustic(fd, shape, n_t, True, ic, np.float64)
+                _ = p.data
+                outcomes.append(("ok", buf.getvalue()))
+            except Exception as e:  # noqa: BLE001 - the message is what is compared
+                outcomes.append((type(e).__name__, str(e)))
+    assert outcomes[0] == outcomes[1]
+    assert outcomes[0][0] != "ok" and "infinite" in outcomes[0][1]
+
+
 def test_fp32_heat_star_kernel(fd):
     shape = (24, 40, 512)
     ic32 = np.random.default_rng(32).random(shape).astype(np.float32)
