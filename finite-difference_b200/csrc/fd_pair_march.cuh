@@ -87,7 +87,7 @@ __device__ __noinline__ uint4 pair_exact_checks(const PairParams<T>& P, int x, i
 // infinite or NaN intermediate (grad, div) always leaves a non-finite stored
 // value behind (inf*c and inf+x are never finite), so a finite sum proves that
 // there is nothing to report.  Only when the sum is not finite are the exact
-// per-value tests run (pair_exact_checks).
+// per-value tests run, after the march (pair_exact_checks).
 #ifndef FD_PAIR_MARCH_BLOCKS
 #define FD_PAIR_MARCH_BLOCKS(T, VY) (sizeof(T) == 8 ? ((VY) == 2 ? 3 : 5) : ((VY) == 2 ? 4 : 5))
 #endif
@@ -107,7 +107,7 @@ pair_march_kernel(const __grid_constant__ PairParams<T> P) {
   const PairAxis<T>& AY = P.ax[1];
   const PairAxis<T>& AZ = P.ax[2];
   unsigned nan_p = 0, nan_x = 0, nan_y = 0, nan_z = 0;
-  bool saw_inf = false;
+  bool saw_inf = false, suspect = false;
   const bool active = vz0 < P.box_hi[2] / VN && y0 + VY <= P.box_hi[1];
 
   if (active) {
@@ -213,15 +213,7 @@ pair_march_kernel(const __grid_constant__ PairParams<T> P) {
         store_vec<T>(oz + r * n2, out_z);
         vxn[r] = next_x;
       }
-      if (!(mag < infinity<T>())) {
-        // something stored is NaN or infinite (or the magnitudes overflowed): exact tests
-        const uint4 c = pair_exact_checks<T, SCALE, VY>(P, x, y0, vz0 * VN);
-        nan_p += c.x & 0xffffu;
-        nan_x += c.y;
-        nan_y += c.z;
-        nan_z += c.w;
-        saw_inf |= (c.x >> 16) != 0;
-      }
+      suspect |= !(mag < infinity<T>());
       ip += plane; ix += plane; iy += plane; iz += plane;
       op += plane; ox += plane; oy += plane; oz += plane;
 #pragma unroll
@@ -231,6 +223,18 @@ pair_march_kernel(const __grid_constant__ PairParams<T> P) {
         pw[2][r] = pw[3][r];
         vx1[r] = vx2[r];
       }
+    }
+  }
+  if (suspect) {
+    // something stored was NaN or infinite (or the magnitudes overflowed): exact
+    // tests over the thread's planes, after the march (nothing is live any more)
+    for (int x = x_begin; x < x_end; ++x) {
+      const uint4 c = pair_exact_checks<T, SCALE, VY>(P, x, y0, vz0 * VN);
+      nan_p += c.x & 0xffffu;
+      nan_x += c.y;
+      nan_y += c.z;
+      nan_z += c.w;
+      saw_inf |= (c.x >> 16) != 0;
     }
   }
   if (saw_inf) raise_flag(P.flags, FD_FLAG_INF);

@@ -10,7 +10,7 @@
 namespace fdb {
 
 // MODE 0: canonical expression, unit spacing, every axis periodic (no range
-//         predicates, no faces)   1: canonical expression,
+//         predicates, no faces)   1: canonical expression, unit spacing,
 //         any boundaries          2: everything decided at run time
 // 3 blocks per SM (<= 80 registers) where that does not spill: 3-point
 // stencils, and the 1-D / 2-D (y-marched) forms of the wider ones
@@ -182,7 +182,7 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
           T acc = (T)0;
 #pragma unroll
           for (int p = 0; p < NP; ++p) acc = add_rn(acc, mul_rn(az.w[p], zw[e / VN][NS * VN - R + e % VN + p]));
-          if (!FAST || P.scale_class) acc = apply_scale(acc, az.div_mode, az.scale, az.inv);
+          if (!FAST) acc = apply_scale(acc, az.div_mode, az.scale, az.inv);
           if (BOUNDED && zbad[e]) acc = quiet_nan<T>();
           saw_inf |= is_inf(acc);
           d[2] = acc;
@@ -191,7 +191,7 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
           T acc = (T)0;
 #pragma unroll
           for (int p = 0; p < NP; ++p) acc = add_rn(acc, mul_rn(ay.w[p], p == R ? center.v[e] : yv[p].v[e]));
-          if (!FAST || P.scale_class) acc = apply_scale(acc, ay.div_mode, ay.scale, ay.inv);
+          if (!FAST) acc = apply_scale(acc, ay.div_mode, ay.scale, ay.inv);
           if (BOUNDED && ybad) acc = quiet_nan<T>();
           saw_inf |= is_inf(acc);
           d[1] = acc;
@@ -200,7 +200,7 @@ star_kernel(const __grid_constant__ StarParams<T> P) {
           T acc = (T)0;
 #pragma unroll
           for (int p = 0; p < NP; ++p) acc = add_rn(acc, mul_rn(ax.w[p], win[(p + u) % NW].v[e]));
-          if (!FAST || P.scale_class) acc = apply_scale(acc, ax.div_mode, ax.scale, ax.inv);
+          if (!FAST) acc = apply_scale(acc, ax.div_mode, ax.scale, ax.inv);
           if (BOUNDED && xbad) acc = quiet_nan<T>();
           saw_inf |= is_inf(acc);
           d[0] = acc;

@@ -23,6 +23,73 @@ __device__ __forceinline__ T lean_scale(T v, const StarAxis<T>& a) {
   return div_invariant(v, a.scale, a.inv);
 }
 
+// Exact NaN count and infinite-der test (FD.py:1112, 528-529) for the points of
+// one thread at plane x, recomputed from the (unchanged) source level.  Rarely
+// executed: out of line, so that the marching loop holds no registers for it.
+// Returns NaN count | inf << 16.
+template <typename T, int R, bool HY, int VY, int VZ, int SCALE, bool PRE>
+__device__ __noinline__ unsigned lean_exact_checks(const StarParams<T>& P, int x, int y0, int vz0) {
+  constexpr int VN = Vec<T>::N;
+  constexpr int NP = 2 * R + 1;
+  const DevFused<T>& F = P.F;
+  const int n[3] = {F.n[0], F.n[1], F.n[2]};
+  unsigned cnt = 0;
+  bool inf = false;
+  for (int r = 0; r < VY; ++r)
+    for (int v = 0; v < VZ; ++v)
+      for (int e = 0; e < VN; ++e) {
+        const int i[3] = {x, y0 + r, (vz0 + 32 * v) * VN + e};
+        const int64_t idx = ((int64_t)i[0] * n[1] + i[1]) * n[2] + i[2];
+        T d[3] = {(T)0, (T)0, (T)0};
+        for (int a = 0; a < 3; ++a) {
+          if (a == 1 && !HY) continue;
+          const StarAxis<T>& A = P.ax[a];
+          const int64_t stride = a == 0 ? (int64_t)n[1] * n[2] : (a == 1 ? n[2] : 1);
+          T acc = (T)0;
+          for (int p = 0; p < NP; ++p) {
+            const int j = wrap_or_clamp(i[a] + p - R, n[a], A.periodic != 0);
+            acc = add_rn(acc, mul_rn(A.w[p], P.src[idx + (int64_t)(j - i[a]) * stride]));
+          }
+          d[a] = lean_scale<T, SCALE>(acc, A);
+          inf |= is_inf(d[a]);
+        }
+        T total;
+        if (HY) {
+          if (PRE) {
+            const T a = mul_rn(d[0], P.pre[0]), b = mul_rn(d[1], P.pre[1]), cz = mul_rn(d[2], P.pre[2]);
+            const T ab = P.subtract[1] ? sub_rn(a, b) : add_rn(a, b);
+            total = P.subtract[2] ? sub_rn(ab, cz) : add_rn(ab, cz);
+          } else {
+            total = add_rn(add_rn(d[0], d[1]), d[2]);
+          }
+        } else if (PRE) {
+          const T a = mul_rn(d[0], P.pre[0]), cz = mul_rn(d[2], P.pre[1]);
+          total = P.subtract[1] ? sub_rn(a, cz) : add_rn(a, cz);
+        } else {
+          total = add_rn(d[0], d[2]);
+        }
+        const T nv = add_rn(P.src[idx], mul_rn(mul_rn(total, P.mul), F.dt));
+        cnt += is_nan(nv) ? 1u : 0u;
+      }
+  return cnt | (inf ? 0x10000u : 0u);
+}
+
+__device__ __forceinline__ float lean_abs(float v) { return fabsf(v); }
+__device__ __forceinline__ double lean_abs(double v) { return fabs(v); }
+__device__ __forceinline__ bool lean_finite(float v) { return v < __int_as_float(0x7f800000); }
+__device__ __forceinline__ bool lean_finite(double v) { return v < __longlong_as_double(0x7ff0000000000000LL); }
+
+// Compile-time experiment, off by default (-DFD_LEAN_TWO_STAGE=1): without BZ
+// the NaN / infinity bookkeeping in two stages, as in the marching pair kernel
+// (fd_pair_march.cuh): every iteration sums the magnitudes of the values it
+// stores; a NaN or infinite der result always leaves a non-finite stored value
+// behind, so a finite sum proves there is nothing to report, and only otherwise
+// are the exact tests run after the march (lean_exact_checks).  It removes 13 of
+// ~112 instructions per iteration, yet 512^3 fp64 runs at 0.401 ms against
+// 0.363 ms with the per-value tests (profiles/lab/ab_two_stage.sh): the
+// dependent magnitude sum and the state kept for the second stage cost more
+// than the DSETPs they replace.  The per-value tests stay.
+//
 // BZ: the contiguous axis is a fixed axis inside the box: outputs outside its
 // [lo, hi) are NaN and its two boundary faces are merged here (a z rim cannot be
 // peeled off as a thin slab without giving up whole 128-bit vector groups).
@@ -32,6 +99,10 @@ __global__ void __launch_bounds__(128, R > 1 ? 4 : ((SCALE == 3 || BZ || PRE) ? 
 star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   constexpr int VN = Vec<T>::N;
   constexpr int NP = 2 * R + 1;
+#ifndef FD_LEAN_TWO_STAGE
+#define FD_LEAN_TWO_STAGE 0
+#endif
+  constexpr bool EXACT = BZ || !FD_LEAN_TWO_STAGE;   // per-value NaN / inf tests inside the loop
   static_assert(R <= VN, "z neighbours come from one vector on each side");
   using PK = Pack<T, VN>;
   const DevFused<T>& F = P.F;
@@ -49,7 +120,7 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
   const StarAxis<T>& ay = P.ax[1];
   const StarAxis<T>& az = P.ax[2];
   unsigned nan_cnt = 0;
-  bool saw_inf = false, clash = false;
+  bool saw_inf = false, clash = false, suspect = false;
   // the launch tiles the box exactly except for the last vector group of a row
   // (VZ == 1 only) and the last row group
   const bool active = (vz0 + 32 * (VZ - 1) < F.box_hi[2] / VN) && (y0 + VY <= F.box_hi[1]);
@@ -87,6 +158,7 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
 
     for (int x = x_begin; x < x_end; ++x) {
       load_plane(win[NP], x + R + 1);
+      T mag = (T)0;                                  // sum of |stored values| (two-stage test)
       PK hm[HY ? R : 1][VZ], hp[HY ? R : 1][VZ];     // rows below / above the thread's rows
       if (HY) {
 #pragma unroll
@@ -126,12 +198,12 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
             for (int p = 0; p < NP; ++p) dz = add_rn(dz, mul_rn(az.w[p], zw[e + p]));
             dz = lean_scale<T, SCALE>(dz, az);
             if (BZ && (j2 < az.lo || j2 >= az.hi)) dz = quiet_nan<T>();
-            saw_inf |= is_inf(dz);
+            if (EXACT) saw_inf |= is_inf(dz);
             T dx = (T)0;
 #pragma unroll
             for (int p = 0; p < NP; ++p) dx = add_rn(dx, mul_rn(ax.w[p], win[p][r][v].v[e]));
             dx = lean_scale<T, SCALE>(dx, ax);
-            saw_inf |= is_inf(dx);
+            if (EXACT) saw_inf |= is_inf(dx);
             T total;
             if (HY) {
               T dy = (T)0;
@@ -143,7 +215,7 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
                 dy = add_rn(dy, mul_rn(ay.w[p], f));
               }
               dy = lean_scale<T, SCALE>(dy, ay);
-              saw_inf |= is_inf(dy);
+              if (EXACT) saw_inf |= is_inf(dy);
               if (PRE) {
                 const T a = mul_rn(dx, P.pre[0]), b = mul_rn(dy, P.pre[1]), cz = mul_rn(dz, P.pre[2]);
                 const T ab = P.subtract[1] ? sub_rn(a, b) : add_rn(a, b);
@@ -170,12 +242,16 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
                   clash |= !is_nan(stored);
               }
             }
-            nan_cnt += is_nan(nv) ? 1u : 0u;
+            if (EXACT)
+              nan_cnt += is_nan(nv) ? 1u : 0u;
+            else
+              mag += lean_abs(nv);
             res.v[e] = nv;
           }
           store_vec<T>(outp + r * n2 + 32 * VN * v, res);
         }
       }
+      if (!EXACT) suspect |= !lean_finite(mag);
       here += plane;
       outp += plane;
 #pragma unroll
@@ -184,6 +260,14 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
         for (int r = 0; r < VY; ++r)
 #pragma unroll
           for (int v = 0; v < VZ; ++v) win[p][r][v] = win[p + 1][r][v];
+    }
+  }
+  if (!EXACT && suspect) {
+    // after the march (nothing is live any more): exact tests over the thread's planes
+    for (int x = x_begin; x < x_end; ++x) {
+      const unsigned c = lean_exact_checks<T, R, HY, VY, VZ, SCALE, PRE>(P, x, y0, vz0);
+      nan_cnt += c & 0xffffu;
+      saw_inf |= (c >> 16) != 0;
     }
   }
   if (saw_inf) raise_flag(F.flags, FD_FLAG_INF);

@@ -542,12 +542,14 @@ class Engine:
                     inner[a][1] = min(inner[a][1], d.rim_hi[a])
         if inner == region:
             return [region]
-        # 3-point statements: the kernels handle a fixed contiguous axis themselves
-        # (a z rim would cost whole vector groups: 2 x 128 of 512 points)
-        if all(d.term[k].st.npts == 3 for k in range(d.nterms)) and d.depth == 1:
-            inner[2] = list(region[2])
-        # otherwise the contiguous axis is processed in whole vector groups
+        # the contiguous axis is processed in whole vector groups
         align = 64 * (16 // self.dtype.itemsize)
+        # 3-point statements: the kernels can handle a fixed contiguous axis
+        # themselves; worth it where a z rim of whole vector groups would be a
+        # large share of the row (2 x 128 of 512 points), not on long rows (8192)
+        if (all(d.term[k].st.npts == 3 for k in range(d.nterms)) and d.depth == 1
+                and 64 * align > region[2][1] - region[2][0]):
+            inner[2] = list(region[2])
         if inner[2] != region[2]:
             lo = -(-inner[2][0] // align) * align
             hi = inner[2][1] // align * align

@@ -130,6 +130,48 @@ def test_history_policies(fd):
             assert np.isnan(got[t]).all()
 
 
+@pytest.mark.parametrize("plant", ["nan", "inf"])
+def test_lean_kernel_two_stage_nan_and_inf(fd, monkeypatch, plant):
+    """The lean star kernel looks for NaN / infinite values through a magnitude
+    sum first and exactly only when that sum is not finite: the growth of a NaN
+    region (values and the 'losing data' note) and the instability error are
+    those of the operator-by-operator path."""
+    shape, n_t = (24, 32, 64), 6
+    ic = np.random.default_rng(14).random(shape)
+    ic[5, 6, 7] = np.nan if plant == "nan" else np.inf
+    outcomes = []
+    for unfused in (False, True):
+        if unfused:
+            monkeypatch.setenv("FD_B200_NO_FUSE", "1")
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            try:
+                axes = {"t": np.arange(n_t) * 1e-3}
+                axes.update({a: np.arange(n) * 1.0 for a, n in zip("xyz", shape)})
+                m = fd.Model(axes, "t", periodic=("x", "y", "z"))
+                T = fd.Field(m, "T", n_time_ders=1)
+                d2 = fd.Stencil([-1, 0, 1], 2)
+                T.set_IC_values(ic)
+                while not m.finished:
+                    T.dot.assign_update(0.1 * ((d2.der(T.prev, "x") + d2.der(T.prev, "y")) + d2.der(T.prev, "z")))
+                    T.time_integrate_update()
+                    m.increment_time()
+                data = T.data
+                outcomes.append(("ok", buf.getvalue().count("losing data"), data))
+                assert unfused or m._engine.stats["fused"] == n_t - 1
+            except AssertionError:
+                raise
+            except Exception as e:  # noqa: BLE001 - the message is what is compared
+                outcomes.append((type(e).__name__, str(e), None))
+    assert outcomes[0][:2] == outcomes[1][:2]
+    if plant == "nan":
+        want, _ = O.run_heat(shape, n_t, True, 0.1, 1e-3, ic)
+        assert outcomes[0][0] == "ok" and outcomes[0][1] >= 1
+        assert np.array_equal(outcomes[0][2], want, equal_nan=True)
+    else:
+        assert "Instability has led to infinite values" in outcomes[0][1]
+
+
 def test_instability_and_override_are_reported(fd):
     with contextlib.redirect_stdout(io.StringIO()):
         m = fd.Model({"t": np.arange(40) * 1.0, "x": np.arange(16) * 1e-3}, "t", periodic=("x",))
