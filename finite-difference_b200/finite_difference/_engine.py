@@ -60,6 +60,7 @@ class FieldState:
         self.halo_ok = [False] * depth    # ghost planes of the slot are current
         self.halo_event = [None] * depth  # ... once this event (comm stream) has completed
         self.wants_ghosts = False         # some statement differentiates this field along the slab axis
+        self.peer = None                  # PeerLinks once mapped, False if peer memory is unavailable
         self.saved = set()                # time indices already in the host history
         self.faces = None                 # {(dim, side): (tensor, per_time_elems or 0)}
         self.counts = engine.dev.zeros_i64(engine.n_t) if self.integrated else None
@@ -228,6 +229,9 @@ class Engine:
         self.overlap = os.environ.get("FD_B200_NO_OVERLAP", "0") != "1"
         self.fuse_pairs = os.environ.get("FD_B200_NO_PAIR", "0") != "1"
         self.fuse_expr = os.environ.get("FD_B200_NO_EXPR", "0") != "1"
+        # halo planes written straight into the neighbours' memory (one NVLink box, NCCL ranks)
+        self.peer_halo = (os.environ.get("FD_B200_NO_P2P", "0") != "1" and self.slab is not None
+                          and self.slab.backend == "nccl" and self.dev.comm_stream is not None)
         points = max([int(np.prod(f._slice_shape)) for f in model.fields] or [1])
         default_poll = 16 if points < (1 << 20) else 64
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
@@ -505,19 +509,42 @@ class Engine:
                 self.stats["halo_exchanges"] = self.stats.get("halo_exchanges", 0) + 1
             return
         import torch
+        if self.peer_halo:
+            for st in states:               # collective set-up, first use only
+                if st.peer is None:
+                    st.peer = self._peer_links(st)
         ready = dev.event()
         ready.record(dev.stream)
         with torch.cuda.stream(dev.comm_stream):
             dev.comm_stream.wait_event(ready)
+            cs = dev.comm_stream.cuda_stream
+            direct = [st for st in states if st.peer]
+            # peer memory: every push first, then the waits (a wait holds the stream)
+            for st in direct:
+                st.peer.push(st.slot_index(t), t + 1, cs)
             for st in states:
-                k = st.slot_index(t)
-                self.slab.exchange(st.ring[k], st.plane, st.owned0, st.H)
+                if not st.peer:
+                    k = st.slot_index(t)
+                    self.slab.exchange(st.ring[k], st.plane, st.owned0, st.H)
+            for st in direct:
+                st.peer.wait(st.slot_index(t), t + 1, self.flags.data_ptr(), cs)
+            if direct:
+                self.stats["peer_halo_exchanges"] = self.stats.get("peer_halo_exchanges", 0) + len(direct)
             done = dev.event()
             done.record(dev.comm_stream)
         for st in states:
             k = st.slot_index(t)
             st.halo_ok[k], st.halo_event[k] = True, done
             self.stats["halo_exchanges"] = self.stats.get("halo_exchanges", 0) + 1
+
+    def _peer_links(self, st):
+        """Map the neighbours' copies of this field's ring (collective); False if
+        any rank could not, in which case the field keeps isend/irecv."""
+        from ._dist import PeerLinks
+        st.peer_flags = self.dev.zeros_i64(2 * len(st.ring))
+        self.dev.synchronize()
+        links = PeerLinks(self.slab, nat, st.ring, st.peer_flags, st.plane * self.dtype.itemsize, st.owned0, st.H)
+        return links if links.ok else False
 
     def _split_boxes(self, d, region):
         """Interior box first, then the rim slabs around it.
@@ -915,6 +942,8 @@ class Engine:
         if self.slab is not None:            # every rank polls at the same steps
             self.slab.all_reduce(self.flags, "max")
         flags = self.flags.cpu().numpy()    # synchronises the compute stream
+        if flags[nat.FD_FLAG_HALO_TIMEOUT]:
+            raise Exception("halo exchange: a neighbouring rank did not deliver its boundary planes in time")
         if flags[nat.FD_FLAG_INF] or flags[nat.FD_FLAG_OVERRIDE]:
             self.flags.zero_()
             if flags[nat.FD_FLAG_INF]:

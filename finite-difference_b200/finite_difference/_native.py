@@ -12,12 +12,14 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 FD_MAX_POINTS = 16
 FD_MAX_TERMS = 4
 FD_MAX_POST = 4
 FD_FLAG_INF = 0
 FD_FLAG_OVERRIDE = 1
+FD_FLAG_HALO_TIMEOUT = 2
+FD_IPC_HANDLE_BYTES = 64
 FD_NUM_FLAGS = 4
 
 # enum fd_ewise_op
@@ -105,6 +107,12 @@ SIGNATURES = {
     "fd_abi_version": (C.c_int, []),
     "fd_last_error": (C.c_char_p, []),
     "fd_launch_count": (C.c_longlong, []),
+    "fd_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_longlong)]),
+    "fd_ipc_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "fd_ipc_close": (C.c_int, [C.c_void_p]),
+    "fd_halo_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p,
+                               C.c_longlong, C.c_void_p]),
+    "fd_halo_wait": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p]),
 }
 for _sfx in ("f64", "f32"):
     SIGNATURES.update({

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define FD_ABI_VERSION 4
+#define FD_ABI_VERSION 5
 
 #define FD_MAX_POINTS 16 /* sample points per stencil                     */
 #define FD_MAX_TERMS 4   /* der() terms summed by one fused statement     */
@@ -45,6 +45,7 @@ extern "C" {
 
 #define FD_FLAG_INF 0
 #define FD_FLAG_OVERRIDE 1
+#define FD_FLAG_HALO_TIMEOUT 2 /* fd_halo_wait gave up (multi-GPU only) */
 #define FD_NUM_FLAGS 4
 
 /* One Stencil applied along one axis: integer index shifts (FD.py:1028-1044),
@@ -292,6 +293,33 @@ typedef struct fd_expr {
 
 int fd_fused_expr_f64(const fd_expr_t* desc, void* stream);
 int fd_fused_expr_f32(const fd_expr_t* desc, void* stream);
+
+/* ---- halo exchange over peer memory (multi-GPU slabs) --------------------
+ *
+ * No reference counterpart: the reference is a single-process numpy program.
+ * These calls replace the isend/irecv pair of finite_difference/_dist.py on one
+ * NVLink/NVSwitch box: neighbouring ranks (one process per GPU) write each
+ * other's ghost planes directly.
+ *
+ * fd_ipc_export: CUDA-IPC handle of the allocation `dev_ptr` lies in (64 bytes
+ *   into handle_out) and the pointer's offset inside it.  The caller ships both
+ *   to the peer process (any host channel).
+ * fd_ipc_open:   maps a peer's allocation into this process (peer access is
+ *   enabled on demand); *base_out + offset is then a device pointer into the
+ *   peer's memory.  Open an allocation once per process.
+ * fd_halo_push:  copies `nbytes` (multiple of 16) from src_lo to peer_dst_lo and
+ *   from src_hi to peer_dst_hi (either side may be NULL/NULL), then stores
+ *   `value` into the peers' flag words with system-scope release semantics.
+ * fd_halo_wait:  one polling thread on `stream` until the int64 words flag_a and
+ *   flag_b (either may be NULL) are >= value; after timeout_ns it raises
+ *   flags[FD_FLAG_HALO_TIMEOUT] and returns instead of hanging. */
+#define FD_IPC_HANDLE_BYTES 64
+int fd_ipc_export(const void* dev_ptr, void* handle_out, long long* offset_out);
+int fd_ipc_open(const void* handle, void** base_out);
+int fd_ipc_close(void* base);
+int fd_halo_push(const void* src_lo, void* peer_dst_lo, const void* src_hi, void* peer_dst_hi, long long nbytes,
+                 void* peer_flag_lo, void* peer_flag_hi, long long value, void* stream);
+int fd_halo_wait(const void* flag_a, const void* flag_b, long long value, long long timeout_ns, void* flags, void* stream);
 
 #ifdef __cplusplus
 }

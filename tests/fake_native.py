@@ -40,7 +40,7 @@ class FakeLib:
         self.error = b""
 
     def fd_abi_version(self):
-        return 4
+        return 5
 
     def fd_last_error(self):
         return self.error
