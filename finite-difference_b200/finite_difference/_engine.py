@@ -229,6 +229,7 @@ class Engine:
         self.overlap = os.environ.get("FD_B200_NO_OVERLAP", "0") != "1"
         self.fuse_pairs = os.environ.get("FD_B200_NO_PAIR", "0") != "1"
         self.fuse_expr = os.environ.get("FD_B200_NO_EXPR", "0") != "1"
+        self.rims_beside = os.environ.get("FD_B200_NO_SIDE_RIMS", "0") != "1"
         # halo planes written straight into the neighbours' memory (one NVLink box, NCCL ranks)
         self.peer_halo = (os.environ.get("FD_B200_NO_P2P", "0") != "1" and self.slab is not None
                           and self.slab.backend == "nccl" and self.dev.comm_stream is not None)
@@ -461,7 +462,9 @@ class Engine:
         if top is not None:
             self.stats["fused_expr"] = self.stats.get("fused_expr", 0) + 1
 
-        def run(piece):
+        def run(piece, on=None):
+            base = on if on is not None else self.dev.stream        # None on the CPU stand-in
+            base_ptr = base.cuda_stream if on is not None else self.stream
             bkey = (id(d), tuple(map(tuple, piece)))
             boxes = self._box_cache.get(bkey)
             if boxes is None:
@@ -472,34 +475,58 @@ class Engine:
                 # the rim slabs read the same level and write disjoint points:
                 # they run beside the interior box instead of after it
                 start = self.dev.event()
-                start.record(self.dev.stream)
+                start.record(base)
                 rim_stream.wait_event(start)
             for i, box in enumerate(boxes):
                 for a in range(3):
                     d.box_lo[a], d.box_hi[a] = box[a]
-                stream = rim_stream.cuda_stream if (i and rim_stream is not None) else self.stream
+                stream = rim_stream.cuda_stream if (i and rim_stream is not None) else base_ptr
                 nat.check(launch(ref, stream))
             if rim_stream is not None:
                 done = self.dev.event()
                 done.record(rim_stream)
-                self.dev.stream.wait_event(done)
+                base.wait_event(done)
 
         # (decided from facts every rank shares: slabs differ in size, collectives must not)
         eager = [ls for ls in levels if ls.H and ls.wants_ghosts and min(self.slab.counts) >= 3 * ls.H]
         if eager and self.overlap:
-            # boundary planes first, their exchange on the comm stream, then the
-            # interior while the planes travel over NVLink
-            lo, hi = region[pad]
-            for cut in ([lo, lo + self.H], [hi - self.H, hi]):
-                run([list(r) if a != pad else cut for a, r in enumerate(region)])
-            self._exchange_ahead(eager, t + 1)
-            run([list(r) if a != pad else [lo + self.H, hi - self.H] for a, r in enumerate(region)])
+            self._run_overlapped(run, region, pad, eager, t)
         else:
             run(region)
         return True
 
-    def _exchange_ahead(self, states, t):
-        """Halo exchange of freshly written boundary planes on the comm stream."""
+    def _run_overlapped(self, run, region, pad, eager, t):
+        """One statement (group) of a slab: the boundary planes and their exchange
+        on the high-priority comm stream, the interior beside them on the compute
+        stream, so that neither the thin boundary launches nor the trip over
+        NVLink add to the step."""
+        lo, hi = region[pad]
+        piece = lambda cut: [list(r) if a != pad else cut for a, r in enumerate(region)]
+        cuts = ([lo, lo + self.H], [hi - self.H, hi])
+        inner = [lo + self.H, hi - self.H]
+        dev = self.dev
+        if dev.comm_stream is None or not self.rims_beside:
+            # (CPU stand-in, or FD_B200_NO_SIDE_RIMS=1) boundary planes first, their
+            # exchange on the comm stream, then the interior while the planes travel
+            for cut in cuts:
+                run(piece(cut))
+            self._exchange_ahead(eager, t + 1)
+            run(piece(inner))
+            return
+        start = dev.event()
+        start.record(dev.stream)
+        dev.comm_stream.wait_event(start)
+        for cut in cuts:
+            run(piece(cut), dev.comm_stream)
+        rims_done = dev.event()
+        rims_done.record(dev.comm_stream)
+        self._exchange_ahead(eager, t + 1, on_comm=True)
+        run(piece(inner))
+        dev.stream.wait_event(rims_done)      # later work on the compute stream sees the whole level
+
+    def _exchange_ahead(self, states, t, on_comm=False):
+        """Halo exchange of freshly written boundary planes on the comm stream
+        (on_comm: the planes were computed on that stream, nothing to wait for)."""
         dev = self.dev
         if dev.comm_stream is None:          # CPU stand-in: same order of operations, synchronously
             for st in states:
@@ -513,10 +540,12 @@ class Engine:
             for st in states:               # collective set-up, first use only
                 if st.peer is None:
                     st.peer = self._peer_links(st)
-        ready = dev.event()
-        ready.record(dev.stream)
+        if not on_comm:
+            ready = dev.event()
+            ready.record(dev.stream)
         with torch.cuda.stream(dev.comm_stream):
-            dev.comm_stream.wait_event(ready)
+            if not on_comm:
+                dev.comm_stream.wait_event(ready)
             cs = dev.comm_stream.cuda_stream
             direct = [st for st in states if st.peer]
             # peer memory: every push first, then the waits (a wait holds the stream)
@@ -716,18 +745,14 @@ class Engine:
             region[pad] = [self.H, self.H + p_state.owned0]
         launch = self._fn["fd_fused_pair"]
 
-        def run(piece):
+        def run(piece, on=None):
             for a in range(3):
                 d.box_lo[a], d.box_hi[a] = piece[a]
-            nat.check(launch(C.byref(d), self.stream))
+            nat.check(launch(C.byref(d), on.cuda_stream if on is not None else self.stream))
 
         eager = [st for st in [p_state] + outs if st.H and st.wants_ghosts and min(self.slab.counts) >= 3 * st.H]
         if eager and self.overlap:
-            lo, hi = region[pad]
-            for cut in ([lo, lo + self.H], [hi - self.H, hi]):
-                run([list(r) if a != pad else cut for a, r in enumerate(region)])
-            self._exchange_ahead(eager, t + 1)
-            run([list(r) if a != pad else [lo + self.H, hi - self.H] for a, r in enumerate(region)])
+            self._run_overlapped(run, region, pad, eager, t)
         else:
             run(region)
         return True
