@@ -28,6 +28,27 @@ def _nccl_options():
     return opts
 
 
+def peer_halo_case(fd, world):
+    """Slabs thick enough for the eager exchange: the boundary planes travel
+    through peer memory (fd_halo_push / fd_halo_wait) unless FD_B200_NO_P2P=1;
+    the gathered result is the single-process oracle's, bit for bit."""
+    import io
+    from oracle import fd_numpy as O
+    from tests.test_gpu_parity import _acoustic, _heat
+    direct = os.environ.get("FD_B200_NO_P2P", "0") != "1"
+    shape, n_t = (8 * world, 24, 64), 12
+    ic = np.random.default_rng(71).random(shape)
+    for periodic in (True, False):
+        m, T = _heat(fd, shape, n_t, periodic, 0.1, 1e-3, ic)
+        want, _ = O.run_heat(shape, n_t, periodic, 0.1, 1e-3, ic)
+        assert np.array_equal(T.data, want, equal_nan=True)
+        assert (m._engine.stats.get("peer_halo_exchanges", 0) >= n_t - 2) == direct, m._engine.stats
+    m, p, v = _acoustic(fd, shape, n_t, True, ic.astype(np.float32), np.float32)
+    want, _ = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic.astype(np.float32), dtype=np.float32)
+    assert np.array_equal(p.data, want.astype(np.float64), equal_nan=True)
+    assert (m._engine.stats.get("peer_halo_exchanges", 0) >= n_t - 2) == direct, m._engine.stats
+
+
 def main():
     backend, names = sys.argv[1], sys.argv[2:]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -45,6 +66,9 @@ def main():
         ctx = fake_native.installed()
     with ctx:
         for name in names:
+            if name == "__peer_halo__":
+                peer_halo_case(fd, world)
+                continue
             results = run_and_compare(name, fd, check_prints=False)
             assert results
     # every rank must have seen a decomposed model

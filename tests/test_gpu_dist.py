@@ -27,3 +27,14 @@ def test_slab_decomposition_nccl_unfused():
     if _gpus() < 2:
         pytest.skip("needs 2 GPUs")
     launch(2, "nccl", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d"], {"FD_B200_NO_FUSE": "1"})
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("direct", [True, False])
+def test_peer_memory_halo_exchange(world, direct):
+    """Boundary planes written straight into the neighbours' ghost planes
+    (CUDA-IPC mapped rings, fd_halo_push / fd_halo_wait) and, with
+    FD_B200_NO_P2P=1, through NCCL isend/irecv: same bits as one process."""
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    launch(world, "nccl", ["__peer_halo__"], {} if direct else {"FD_B200_NO_P2P": "1"})
