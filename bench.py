@@ -314,7 +314,7 @@ def run_b200(args):
     torch.cuda.empty_cache()
 
     # ---- end to end through the public API with host buffers -------------
-    result_pinned = torch.empty_like(pinned)     # host buffer for the result, like `pinned` for the input
+    result_pinned = torch.empty(pinned.shape, dtype=pinned.dtype, pin_memory=True)   # (empty_like would not be pinned)
     result = result_pinned.numpy().reshape(shape)
 
     def end_to_end(steps):
@@ -353,8 +353,10 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f32" if np_dtype == np.float32 else "f64", "data": "synthetic",
         "config": {"workload": desc, "grid_per_gpu": "x".join(map(str, shape)),
                    "l2": "inputs larger than L2 (state level = %.0f MiB vs 126 MB L2)" % (bytes_level / 2 ** 20),
-                   "multi_gpu": (f"slab decomposition along x over {world} ranks, NCCL send/recv halo exchange every step"
-                                 if world > 1 else "single GPU"),
+                   "multi_gpu": (f"slab decomposition along x over {world} ranks, halo planes "
+                                 + ("written into the neighbours' memory over NVLink (peer-memory push + flag words)"
+                                    if stats.get("peer_halo_exchanges") else "exchanged with NCCL send/recv")
+                                 + " every step" if world > 1 else "single GPU"),
                    "history": "last", "engine_stats": stats},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(args.workload), "peak_source": peak_src,

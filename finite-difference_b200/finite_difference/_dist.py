@@ -8,9 +8,11 @@ on the slab's coordinates, and ``Field.data`` gathers the global array.
 
 On the device a level is stored with ``H`` ghost planes on either side of the
 owned planes (``H`` = largest stencil reach along the slab axis).  Before a
-level is differentiated along the slab axis its ghost planes are refreshed
-with one ``isend/irecv`` pair per neighbour (NCCL over NVLink on the GPU box,
-gloo in the CPU tests); planes are contiguous in memory, so nothing is packed.
+level is differentiated along the slab axis its ghost planes are refreshed:
+on the GPU box the neighbours write them straight into this rank's memory
+over NVLink (``PeerLinks`` below, csrc/fd_halo.cu); where that is not possible
+-- and in the CPU tests (gloo) -- with one ``isend/irecv`` pair per neighbour.
+Planes are contiguous in memory, so nothing is packed.
 The kernels then see a non-periodic axis whose valid range is the owned planes
 (``fd_fused_t.range_*``), which keeps the arithmetic -- and therefore the
 results -- identical to the single-GPU run.
