@@ -98,3 +98,43 @@ def test_staggered_pair_with_guard_zones(dtype, march, monkeypatch):
     want, _ = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic, dtype=dtype)
     assert np.array_equal(got, want.astype(np.float64), equal_nan=True)
     assert m._engine.stats.get("fused_pairs") == n_t - 1
+
+
+def test_halo_push_and_wait_on_one_gpu():
+    """fd_halo_push / fd_halo_wait through the C ABI with both 'peers' on this
+    GPU: planes copied, level number published after the copy, the wait returns
+    once both flag words have reached it, and gives up with
+    FD_FLAG_HALO_TIMEOUT (instead of hanging) when a neighbour never delivers."""
+    import ctypes as C
+    import torch
+    from finite_difference import _native as nat
+    lib = nat.lib
+    plane = 96 * 130
+    src = torch.arange(4 * plane, dtype=torch.float64, device="cuda")
+    dst = torch.full((4 * plane,), -1.0, dtype=torch.float64, device="cuda")
+    flags = torch.zeros(4, dtype=torch.int64, device="cuda")
+    err = torch.zeros(nat.FD_NUM_FLAGS, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    base_s, base_d, f = src.data_ptr(), dst.data_ptr(), flags.data_ptr()
+    nbytes = plane * 8
+    # low side: plane 1 -> plane 3 of dst; high side: plane 2 -> plane 0 of dst
+    nat.check(lib.fd_halo_push(base_s + nbytes, base_d + 3 * nbytes, base_s + 2 * nbytes, base_d, nbytes, f, f + 8, 7, stream))
+    nat.check(lib.fd_halo_wait(f, f + 8, 7, 2_000_000_000, err.data_ptr(), stream))
+    torch.cuda.synchronize()
+    assert flags.tolist() == [7, 7, 0, 0] and err.tolist() == [0] * nat.FD_NUM_FLAGS
+    assert torch.equal(dst[3 * plane:], src[plane:2 * plane]) and torch.equal(dst[:plane], src[2 * plane:3 * plane])
+    assert bool((dst[plane:3 * plane] == -1.0).all())
+    # one-sided (end rank of a fixed slab axis): only the high side exists
+    nat.check(lib.fd_halo_push(None, None, base_s, base_d + nbytes, nbytes, None, f + 16, 9, stream))
+    nat.check(lib.fd_halo_wait(None, f + 16, 9, 2_000_000_000, err.data_ptr(), stream))
+    torch.cuda.synchronize()
+    assert flags.tolist() == [7, 7, 9, 0] and torch.equal(dst[plane:2 * plane], src[:plane])
+    # an older level number is already satisfied; a newer one that never comes times out
+    nat.check(lib.fd_halo_wait(f, f + 8, 5, 2_000_000_000, err.data_ptr(), stream))
+    nat.check(lib.fd_halo_wait(f, f + 24, 8, 20_000_000, err.data_ptr(), stream))
+    torch.cuda.synchronize()
+    assert err.tolist()[nat.FD_FLAG_HALO_TIMEOUT] != 0 and err.tolist()[nat.FD_FLAG_INF] == 0
+    # argument checks
+    assert lib.fd_halo_push(base_s, base_d, None, None, 24, None, None, 1, stream) != 0
+    assert b"multiple of 16" in lib.fd_last_error()
+    assert lib.fd_halo_push(base_s, None, None, None, 32, None, None, 1, stream) != 0
