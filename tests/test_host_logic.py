@@ -126,3 +126,111 @@ def test_time_varying_coefficient_does_not_reuse_a_stale_plan():
         lap = O.der(want[t], [-1, 0, 1], w, 2, 0, True, False, False, 1.0)
         want[t + 1] = want[t] + ((0.1 + 0.05 * t) * lap) * 0.01
     assert np.array_equal(got, want)
+
+
+def test_peer_links_address_arithmetic():
+    """PeerLinks (peer-memory halo exchange) with stand-ins for the C ABI and the
+    process group: slabs of unequal thickness, fixed and periodic slab axes, and
+    world 2 where both neighbours are the same rank.  Checked: which planes are
+    sent where, which flag words are written and awaited."""
+    import ctypes as C
+    from finite_difference import _dist
+
+    class T:                                   # a 'device tensor'
+        def __init__(self, addr):
+            self.addr = addr
+
+        def data_ptr(self):
+            return self.addr
+
+    class Lib:                                 # allocation r*2^32 holds everything rank r exports
+        def __init__(self, rank, calls):
+            self.rank, self.calls = rank, calls
+
+        def fd_ipc_export(self, ptr, handle, off):
+            handle.raw = bytes([ptr >> 32]) * 64
+            off._obj.value = ptr & 0xffffffff
+            return 0
+
+        def fd_ipc_open(self, handle, base):
+            owner = handle[0]
+            assert owner != self.rank
+            base._obj.value = (owner << 32) + 0x7000_0000_0000       # mapped somewhere else in this process
+            return 0
+
+        def fd_halo_push(self, *a):
+            self.calls.append(("push",) + a)
+            return 0
+
+        def fd_halo_wait(self, *a):
+            self.calls.append(("wait",) + a)
+            return 0
+
+    class Nat:
+        FD_IPC_HANDLE_BYTES = 64
+        NativeError = RuntimeError
+
+        def __init__(self, rank, calls):
+            self.lib = Lib(rank, calls)
+
+        @staticmethod
+        def check(rc):
+            assert rc == 0
+
+    class Dist:
+        def __init__(self, world, table):
+            self.world, self.table = world, table
+
+        def all_gather_object(self, out, mine):
+            out[:] = self.table.pop(0)(mine)
+
+    plane_bytes, H = 4096, 2
+    for world, periodic, counts in [(3, False, [5, 4, 4]), (3, True, [5, 4, 4]), (2, True, [6, 6])]:
+        ring_addr = lambda r, k: (r << 32) + 0x10000 * (k + 1)
+        flag_addr = lambda r: (r << 32) + 0x80000
+        exports = []
+        for r in range(world):                                     # what every rank would publish
+            exports.append({"ring": [(bytes([r]) * 64, ring_addr(r, k) & 0xffffffff) for k in range(2)],
+                            "flags": (bytes([r]) * 64, flag_addr(r) & 0xffffffff), "owned0": counts[r]})
+        for r in range(world):
+            _dist.PeerLinks._opened = {}
+            calls = []
+
+            class Slab:
+                pass
+            slab = Slab()
+            slab.world, slab.rank = world, r
+            slab.prev_rank = (r - 1) % world if (periodic or r > 0) else None
+            slab.next_rank = (r + 1) % world if (periodic or r < world - 1) else None
+
+            def gather_entries(mine, r=r):
+                assert mine == exports[r]
+                return list(exports)
+            slab.dist = Dist(world, [gather_entries, lambda ok: [ok] * world])
+            links = _dist.PeerLinks(slab, Nat(r, calls), [T(ring_addr(r, 0)), T(ring_addr(r, 1))], T(flag_addr(r)),
+                                    plane_bytes, counts[r], H)
+            assert links.ok and links.nbytes == H * plane_bytes
+            mapped = lambda q, addr: addr + 0x7000_0000_0000
+            for k in range(2):
+                links.push(k, 11, 0)
+                links.wait(k, 11, 123, 0)
+                push, wait = calls[-2], calls[-1]
+                prev, nxt = slab.prev_rank, slab.next_rank
+                base = ring_addr(r, k)
+                want_push = (
+                    base + H * plane_bytes if prev is not None else None,                                   # my low owned planes
+                    mapped(prev, ring_addr(prev, k)) + (H + counts[prev]) * plane_bytes if prev is not None else None,  # prev's high ghosts
+                    base + counts[r] * plane_bytes if nxt is not None else None,                          # my high owned planes
+                    mapped(nxt, ring_addr(nxt, k)) if nxt is not None else None,                          # next's low ghosts
+                    H * plane_bytes,
+                    mapped(prev, flag_addr(prev)) + (2 * k + 1) * 8 if prev is not None else None,        # "your high ghost is fresh"
+                    mapped(nxt, flag_addr(nxt)) + (2 * k) * 8 if nxt is not None else None,               # "your low ghost is fresh"
+                    11, 0)
+                assert push[1:] == want_push
+                assert wait[1:] == (flag_addr(r) + 2 * k * 8 if prev is not None else None,
+                                    flag_addr(r) + (2 * k + 1) * 8 if nxt is not None else None, 11, links.TIMEOUT_NS, 123, 0)
+    # planes that are not multiples of 16 bytes: the field keeps isend/irecv, on every rank
+    slab = Slab()
+    slab.world, slab.rank, slab.prev_rank, slab.next_rank = 2, 0, 1, 1
+    slab.dist = Dist(2, [lambda mine: [mine, {"ring": [], "flags": None, "owned0": 4}], lambda ok: [ok, True]])
+    assert not _dist.PeerLinks(slab, Nat(0, []), [T(0x10000)], T(0x80000), 360, 4, 1).ok
