@@ -182,11 +182,13 @@ fused_vec_kernel(const __grid_constant__ DevFused<T> P) {
 #pragma unroll
     for (int l = 0; l < 2; ++l) {
       if (l < P.depth) {
-        const PK pv = load_vec<T>(P.prev[l] + idx0);
+        const bool assigned = l == 0 && !P.prev[0];     // level 0 is the assigned field itself
+        PK pv = rate;
+        if (!assigned) pv = load_vec<T>(P.prev[l] + idx0);
         PK nv;
 #pragma unroll
         for (int e = 0; e < VN; ++e) {
-          T v = add_rn(pv.v[e], mul_rn(rate.v[e], P.dt));
+          T v = assigned ? rate.v[e] : add_rn(pv.v[e], mul_rn(rate.v[e], P.dt));
           if (rim_row || (rim_z && (i2 + e == P.rim_lo[2] || i2 + e == P.rim_hi[2]))) {
             const T stored = stored_face_value(P, l, i0, i1, i2 + e);
             if (is_nan(v))

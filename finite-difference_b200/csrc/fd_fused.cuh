@@ -162,7 +162,8 @@ inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P, int min_terms = 1
     P->prev[l] = (const T*)d->prev[l];
     P->out[l] = (T*)d->out[l];
     P->nan_count[l] = (long long*)d->nan_count[l];
-    if (l < d->depth && (!d->prev[l] || !d->out[l]))
+    // prev[0] == NULL: level 0 is the assigned field itself (no Euler step)
+    if (l < d->depth && (!d->out[l] || (!d->prev[l] && l != 0)))
       return fail("fd_fused_step: level %d needs prev and out", l);
     for (int a = 0; a < 3; ++a)
       for (int s = 0; s < 2; ++s) {
@@ -236,7 +237,7 @@ __device__ __forceinline__ void fused_epilogue(const DevFused<T>& P, T rhs, int6
 #pragma unroll
   for (int l = 0; l < 2; ++l) {
     if (l < P.depth) {
-      T v = add_rn(__ldg(P.prev[l] + idx), mul_rn(rate, P.dt));
+      T v = (l == 0 && !P.prev[0]) ? rate : add_rn(__ldg(P.prev[l] + idx), mul_rn(rate, P.dt));
       if (rim) {
         const T stored = stored_face_value(P, l, i0, i1, i2);
         if (is_nan(v))

@@ -17,6 +17,7 @@ int try_star(const DevFused<T>& F, cudaStream_t stream) {
   StarParams<T> P;
   int R = 0, axes = 0;
   int mode = 2;
+  if (!F.prev[0]) return 0;     // assign_update without an Euler chain: general kernels
   if (!star_applicable<T>(F, &P, &R, &axes, &mode)) return 0;
   if ((int64_t)F.n[1] > 65535LL * 8) return 0;
   switch (R) {

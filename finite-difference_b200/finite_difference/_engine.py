@@ -230,6 +230,7 @@ class Engine:
         self.fuse_pairs = os.environ.get("FD_B200_NO_PAIR", "0") != "1"
         self.fuse_expr = os.environ.get("FD_B200_NO_EXPR", "0") != "1"
         self.rims_beside = os.environ.get("FD_B200_NO_SIDE_RIMS", "0") != "1"
+        self.fuse_aux = os.environ.get("FD_B200_NO_AUX", "0") != "1"
         # halo planes written straight into the neighbours' memory (one NVLink box, NCCL ranks)
         self.peer_halo = (os.environ.get("FD_B200_NO_P2P", "0") != "1" and self.slab is not None
                           and self.slab.backend == "nccl" and self.dev.comm_stream is not None)
@@ -289,8 +290,10 @@ class Engine:
             if i in consumed:
                 continue
             if kind == "assign":
+                # (an empty chain: an auxiliary field such as a flux, or a .dot that
+                # is not integrated in this step -- the statement is still one launch)
                 chain = self._find_chain(stmts, i, field)
-                if self.fuse and chain and self._try_fused(field, node, chain, t, reads_new):
+                if self.fuse and (chain or self.fuse_aux) and self._try_fused(field, node, chain, t, reads_new):
                     consumed.update(j for j, _ in chain)
                     self.stats["fused"] += 1
                     continue
@@ -324,7 +327,10 @@ class Engine:
         step ``t``; returns None when the statement needs the unfused operators."""
         dot_state = self.state(dot_field)
         dims3 = dot_state.dims3
-        if dims3 is None or dot_field._bc_locations:
+        # no chain: the assign_update alone (an auxiliary field such as a flux, or a
+        # .dot that is not integrated in this step); its own faces are merged
+        aux = not chain
+        if dims3 is None or (dot_field._bc_locations and not aux):
             return None
         matched = _match_statement(node)
         program = None
@@ -337,7 +343,7 @@ class Engine:
             terms, posts = [(der, False, None, False) for der in program[0]], []
         else:
             terms, posts = matched
-        levels = [self.state(p) for _, p in chain]
+        levels = [self.state(p) for _, p in chain] if chain else [dot_state]
         if any(ls.field._slice_shape != dot_field._slice_shape for ls in levels):
             return None
         if node.shape != tuple(dot_field._slice_shape):
@@ -403,11 +409,13 @@ class Engine:
                 except RuntimeError:
                     return None
                 sources.append((self.state(leaf.field), leaf.t - t, False))
+        if any(src_state is dot_state for src_state, _, _ in sources):
+            return None          # the target's single slot would be read while it is written
         d.depth = len(levels)
         d.dt = float(self.model.dt)
         dyn_faces = []
         for l, ls in enumerate(levels):
-            d.prev[l] = ls.level(t).data_ptr()
+            d.prev[l] = 0 if aux else ls.level(t).data_ptr()      # 0: level 0 is the assigned field itself
             d.out[l] = ls.ring[ls.slot_index(t + 1)].data_ptr()
             for (dim, side), (_, per_time) in ls.face_items():
                 d.face[l][dim + pad][side] = ls.face_ptr(dim, side, t + 1)
@@ -418,7 +426,7 @@ class Engine:
             d.rim_lo[a], d.rim_hi[a] = 0, max(dims3[a] - 1, 0)
         if self.H:
             d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
-        return d, dot_state, levels, sources, dyn_faces, pad, dims3, top
+        return d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux
 
     def _try_fused(self, dot_field, node, chain, t, reads_new):
         # the same statement comes back every step: its launch descriptor is
@@ -433,7 +441,7 @@ class Engine:
                 self._plans.clear()
                 self._box_cache.clear()
             self._plans[key] = plan
-        d, dot_state, levels, sources, dyn_faces, pad, dims3, top = plan
+        d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux = plan
         for src_state, offset, slab in sources:
             try:
                 src_state.level(t + offset)
@@ -442,14 +450,18 @@ class Engine:
                 return False
             if slab:
                 src_state.refresh_ghosts(t + offset)
-        want_dot = id(dot_field) in reads_new or self.wants_level(t + 1)
-        d.dot_out = dot_state.claim(t + 1).data_ptr() if want_dot else 0
-        if not want_dot:
-            dot_state.held[0] = -1
-        for l, ls in enumerate(levels):
-            ls.level(t)
-            ls.claim(t + 1)
-            d.nan_count[l] = ls.counts.data_ptr() + 8 * (t + 1)
+        if aux:
+            d.dot_out = 0
+            d.out[0] = dot_state.claim(t + 1).data_ptr()
+        else:
+            want_dot = id(dot_field) in reads_new or self.wants_level(t + 1)
+            d.dot_out = dot_state.claim(t + 1).data_ptr() if want_dot else 0
+            if not want_dot:
+                dot_state.held[0] = -1
+            for l, ls in enumerate(levels):
+                ls.level(t)
+                ls.claim(t + 1)
+                d.nan_count[l] = ls.counts.data_ptr() + 8 * (t + 1)
         for l, dim3, side, ls, dim in dyn_faces:
             d.face[l][dim3][side] = ls.face_ptr(dim, side, t + 1)
         region = [[0, dims3[a]] for a in range(3)]
@@ -490,12 +502,15 @@ class Engine:
         # (decided from facts every rank shares: slabs differ in size, collectives must not)
         eager = [ls for ls in levels if ls.H and ls.wants_ghosts and min(self.slab.counts) >= 3 * ls.H]
         if eager and self.overlap:
-            self._run_overlapped(run, region, pad, eager, t)
+            # peer-memory pushes need the statement itself to read the level-t ghosts
+            # of the field it advances (see _exchange_ahead)
+            own = {id(st) for st, offset, slab in sources if slab and offset == 0}
+            self._run_overlapped(run, region, pad, eager, t, {id(ls) for ls in eager if id(ls) in own and not aux})
         else:
             run(region)
         return True
 
-    def _run_overlapped(self, run, region, pad, eager, t):
+    def _run_overlapped(self, run, region, pad, eager, t, direct_ok=()):
         """One statement (group) of a slab: the boundary planes and their exchange
         on the high-priority comm stream, the interior beside them on the compute
         stream, so that neither the thin boundary launches nor the trip over
@@ -510,7 +525,7 @@ class Engine:
             # exchange on the comm stream, then the interior while the planes travel
             for cut in cuts:
                 run(piece(cut))
-            self._exchange_ahead(eager, t + 1)
+            self._exchange_ahead(eager, t + 1, direct_ok=direct_ok)
             run(piece(inner))
             return
         start = dev.event()
@@ -520,13 +535,23 @@ class Engine:
             run(piece(cut), dev.comm_stream)
         rims_done = dev.event()
         rims_done.record(dev.comm_stream)
-        self._exchange_ahead(eager, t + 1, on_comm=True)
+        self._exchange_ahead(eager, t + 1, on_comm=True, direct_ok=direct_ok)
         run(piece(inner))
         dev.stream.wait_event(rims_done)      # later work on the compute stream sees the whole level
 
-    def _exchange_ahead(self, states, t, on_comm=False):
+    def _exchange_ahead(self, states, t, on_comm=False, direct_ok=()):
         """Halo exchange of freshly written boundary planes on the comm stream
-        (on_comm: the planes were computed on that stream, nothing to wait for)."""
+        (on_comm: the planes were computed on that stream, nothing to wait for).
+
+        direct_ok: states that may be written straight into the neighbours' ghost
+        planes.  A push is not a rendezvous: nothing stops a neighbour from
+        delivering level t+2 into the slot whose level-t ghosts this rank is
+        still reading -- unless the statement that produces a level also reads
+        the previous level's ghosts of the same field.  Then a neighbour can only
+        produce (and push) level t+2 after it has received this rank's level t+1
+        planes, which are pushed after the boundary kernels that read the level-t
+        ghosts.  Heat/wave statements and the staggered pair have that form; any
+        other field is exchanged with isend/irecv, which is a rendezvous."""
         dev = self.dev
         if dev.comm_stream is None:          # CPU stand-in: same order of operations, synchronously
             for st in states:
@@ -538,7 +563,7 @@ class Engine:
         import torch
         if self.peer_halo:
             for st in states:               # collective set-up, first use only
-                if st.peer is None:
+                if st.peer is None and id(st) in direct_ok and len(st.ring) > 1:
                     st.peer = self._peer_links(st)
         if not on_comm:
             ready = dev.event()
@@ -547,12 +572,12 @@ class Engine:
             if not on_comm:
                 dev.comm_stream.wait_event(ready)
             cs = dev.comm_stream.cuda_stream
-            direct = [st for st in states if st.peer]
+            direct = [st for st in states if st.peer and id(st) in direct_ok]
             # peer memory: every push first, then the waits (a wait holds the stream)
             for st in direct:
                 st.peer.push(st.slot_index(t), t + 1, cs)
             for st in states:
-                if not st.peer:
+                if st not in direct:
                     k = st.slot_index(t)
                     self.slab.exchange(st.ring[k], st.plane, st.owned0, st.H)
             for st in direct:
@@ -752,7 +777,8 @@ class Engine:
 
         eager = [st for st in [p_state] + outs if st.H and st.wants_ghosts and min(self.slab.counts) >= 3 * st.H]
         if eager and self.overlap:
-            self._run_overlapped(run, region, pad, eager, t)
+            # (the pair kernel reads the level-t ghosts of p and of the slab-axis velocity)
+            self._run_overlapped(run, region, pad, eager, t, {id(st) for st in eager})
         else:
             run(region)
         return True

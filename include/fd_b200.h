@@ -181,12 +181,15 @@ typedef struct fd_post {
  *   dot_out   = rhs                     (optional)   FD.py:478-498
  *   out[0]    = merge(prev[0] + rhs*dt,    faces[0]) FD.py:500-538, 541-576
  *   out[1]    = merge(prev[1] + out[0]*dt, faces[1]) (depth == 2)
+ * prev[0] == NULL is the assign_update alone (an auxiliary field such as a flux,
+ * or a .dot that is not integrated in this step; FD.py:478-498 with the store of
+ * FD.py:541-576):  out[0] = merge(rhs, faces[0]),  depth = 1, dot_out unused.
  * Boundary faces hold the values the reference pre-populates at time t+1 with
  * set_BC (FD.py:361-385); face[l][d][side] is an array over the two other
  * dimensions in order, or NULL.  Periodic axes wrap the index in-kernel,
  * fixed axes predicate on [lo, hi).
  * Multi-GPU: a slab carries ghost planes along its decomposed dimension; the
- * caller exchanges them (NCCL send/recv), describes that dimension as
+ * caller exchanges them (fd_halo_push below, or send/recv), describes that dimension as
  * non-periodic with [lo, hi) = the planes it owns and restricts execution
  * with box_lo / box_hi. */
 typedef struct fd_fused {
@@ -194,7 +197,7 @@ typedef struct fd_fused {
   int32_t nterms;
   fd_term_t term[FD_MAX_TERMS];
   int32_t npost;
-  int32_t depth;
+  int32_t depth;      /* 1 or 2 stored levels */
   fd_post_t post[FD_MAX_POST];
   double dt;
   void* dot_out;

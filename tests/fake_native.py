@@ -172,7 +172,7 @@ class FakeLib:
             _arr(d.dot_out, size).reshape(n)[region] = total[region]
         rate = total
         for l in range(d.depth):
-            new = _arr(d.prev[l], size).reshape(n) + rate * d.dt
+            new = _arr(d.prev[l], size).reshape(n) + rate * d.dt if d.prev[l] else np.array(rate, dtype=float)
             stored = np.full(n, np.nan)
             for dim in range(3):
                 for side in range(2):

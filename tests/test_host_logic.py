@@ -234,3 +234,26 @@ def test_peer_links_address_arithmetic():
     slab.world, slab.rank, slab.prev_rank, slab.next_rank = 2, 0, 1, 1
     slab.dist = Dist(2, [lambda mine: [mine, {"ring": [], "flags": None, "owned0": 4}], lambda ok: [ok, True]])
     assert not _dist.PeerLinks(slab, Nat(0, []), [T(0x10000)], T(0x80000), 360, 4, 1).ok
+
+
+def test_auxiliary_assign_is_fused():
+    """An assign_update that no time_integrate_update follows (auxiliary flux
+    field with boundary faces) is one fused launch: no statement
+    of the flux scenario takes the operator-by-operator path."""
+    import finite_difference.model as M
+    engines = []
+    orig = M.Model._get_engine
+
+    def spy(self):
+        e = orig(self)
+        if e not in engines:
+            engines.append(e)
+        return e
+
+    M.Model._get_engine = spy
+    try:
+        with fake_native.installed():
+            run_and_compare("flux_1d", fd)
+    finally:
+        M.Model._get_engine = orig
+    assert engines and all(e.stats["unfused_statements"] == 0 and e.stats["fused"] == 10 for e in engines)
