@@ -77,50 +77,100 @@ def recorded_traffic(workload):
 
 
 class ClockSampler:
-    """nvidia-smi clocks and throttle reasons during the timed region."""
+    """SM clock and throttle reasons during the timed region.
+
+    NVML in-process (a thread polling every 2 ms: the timed region of the default
+    run is only ~40 ms long, shorter than the start-up of an nvidia-smi process);
+    `nvidia-smi -lms` as the fallback when the NVML binding is unavailable."""
     QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    NVML_BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, index=0):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+        self.nvml, self.handle, self.stop, self.source = None, None, threading.Event(), None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        handle = None
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            handle = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+        except Exception:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+        pynvml.nvmlDeviceGetClockInfo(handle, pynvml.NVML_CLOCK_SM)       # fails here rather than in the thread
+        return pynvml, handle
 
     def __enter__(self):
+        try:
+            self.nvml, self.handle = self._nvml_handle()
+            self.source = "nvml"
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return self
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100",
                  "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.source = "nvidia-smi"
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except OSError:
             self.proc = None
         return self
 
+    def _poll_nvml(self):
+        n = self.nvml
+        try:
+            mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+        except Exception:
+            mx = None
+        while not self.stop.is_set():
+            try:
+                sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                try:
+                    mask = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                except Exception:
+                    mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.rows.append([str(sm), str(mx if mx is not None else sm)]
+                                 + ["Active" if mask & self.NVML_BITS[k] else "Not Active" for k in self.NAMES])
+            except Exception:
+                pass
+            self.stop.wait(0.002)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def __exit__(self, *exc):
-        if self.proc is not None:
+        if self.nvml is not None:
+            self.stop.set()
+            self.thread.join(timeout=2)
+        elif self.proc is not None:
             time.sleep(0.15)
             self.proc.terminate()
             self.thread.join(timeout=2)
 
     def summary(self):
         sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             try:
                 sm.append(float(r[0]))
                 mx.append(float(r[1]))
             except (ValueError, IndexError):
                 continue
-            for name, v in zip(names, r[2:6]):
+            for name, v in zip(self.NAMES, r[2:6]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": self.source}
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": self.source}
 
 
 # ---------------------------------------------------------- the B200 model
