@@ -17,6 +17,10 @@ extern std::atomic<long long> g_launches;
 
 int fail(const char* fmt, ...);
 
+// fd_last_kernel(): which kernel a fused entry point chose, and its geometry
+extern thread_local char g_kernel[192];
+void note_kernel(const char* fmt, ...);
+
 inline int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail("%s: %s", what, cudaGetErrorString(e));

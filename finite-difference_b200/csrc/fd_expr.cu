@@ -163,6 +163,8 @@ static int expr_impl(const fd_expr_t* d, void* stream) {
   while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.F.x_chunk = chunk;
   dim3 grid((n2 + bx - 1) / bx, (unsigned)gy, (nx + chunk - 1) / chunk), block(bx, by, 1);
+  note_kernel("expr f%d code=%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, P.ncode, chunk, grid.x, grid.y, grid.z,
+              bx, by);
   expr_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(P);
   return check_launch("fd_fused_expr");
 }

@@ -274,6 +274,7 @@ static int fused_impl(const fd_fused_t* d, void* stream) {
       while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
       P.x_chunk = chunk;
       dim3 grid((nv + bx - 1) / bx, (unsigned)gy, (nx + chunk - 1) / chunk), block(bx, by, 1);
+      note_kernel("fused_vec f%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, chunk, grid.x, grid.y, grid.z, bx, by);
       fused_vec_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(P);
       return check_launch("fd_fused_step(vector)");
     }
@@ -295,6 +296,7 @@ static int fused_impl(const fd_fused_t* d, void* stream) {
   while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.x_chunk = chunk;
   dim3 grid((n2 + bx - 1) / bx, (unsigned)gy, (nx + chunk - 1) / chunk);
+  note_kernel("fused f%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, chunk, grid.x, grid.y, grid.z, bx, by);
   fused_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(P);
   return check_launch("fd_fused_step");
 }

@@ -24,6 +24,15 @@ int fail(const char* fmt, ...) {
   return 1;
 }
 
+thread_local char g_kernel[192] = "";
+
+void note_kernel(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_kernel, sizeof(g_kernel), fmt, ap);
+  va_end(ap);
+}
+
 constexpr int kThreads = 256;
 
 static inline unsigned blocks_for(int64_t n, int per_block) {
@@ -238,6 +247,7 @@ extern "C" {
 int fd_abi_version(void) { return FD_ABI_VERSION; }
 const char* fd_last_error(void) { return g_err; }
 long long fd_launch_count(void) { return g_launches.load(); }
+const char* fd_last_kernel(void) { return g_kernel; }
 
 int fd_der_f64(void* dst, const void* src, int64_t outer, int64_t n_src, int64_t n_dst,
                int64_t inner, const fd_stencil_t* st, int periodic, int64_t lo, int64_t hi,

@@ -254,6 +254,8 @@ static int pair_impl(const fd_pair_t* d, void* stream) {
     for (int a = 0; a < d->naxes; ++a) any_dot |= d->ax[a].vdot_out != nullptr;
     if (try_pair_march<T>(P, d->naxes, any_dot, scale_class, st)) return check_launch("fd_fused_pair(march)");
   }
+  note_kernel("pair f%d axes=%d scale=%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, d->naxes, scale_class, chunk,
+              grid.x, grid.y, grid.z, bx, by);
 #define FD_PAIR(NA)                                                        \
   if (scale_class == 0)                                                    \
     pair_kernel<T, NA, 0><<<grid, block, 0, st>>>(P);                      \

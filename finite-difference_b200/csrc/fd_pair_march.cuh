@@ -293,6 +293,8 @@ bool try_pair_march(PairParams<T>& P, int naxes, bool any_dot, int scale_class, 
   while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.x_chunk = chunk;
   dim3 grid((nv + 31) / 32, (groups + by - 1) / by, (nx + chunk - 1) / chunk), block(32, by, 1);
+  note_kernel("pair_march f%d vy=%d scale=%d chunk=%d grid=%ux%ux%u block=32x%d", (int)sizeof(T) * 8, vy, scale_class, chunk,
+              grid.x, grid.y, grid.z, by);
 #define FD_MARCH(SC)                                             \
   if (vy == 2)                                                   \
     pair_march_kernel<T, SC, 2><<<grid, block, 0, stream>>>(P);  \

@@ -321,6 +321,8 @@ static void launch_star_vpt(StarParams<T>& P, int bx, int by, cudaStream_t strea
   while ((n0 + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.x_chunk = chunk;
   dim3 grid(gx, gy, (n0 + chunk - 1) / chunk), block(bx, by, 1);
+  note_kernel("star f%d R=%d axes=%d mode=%d vpt=%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, R, AXES, MODE,
+              VPT, chunk, grid.x, grid.y, grid.z, bx, by);
   star_kernel<T, R, AXES, MODE, VPT><<<grid, block, 0, stream>>>(P);
 }
 

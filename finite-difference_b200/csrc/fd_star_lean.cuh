@@ -277,6 +277,9 @@ star_lean_kernel(const __grid_constant__ StarParams<T> P) {
 
 template <typename T, int R, bool HY, int VY, int VZ>
 static void launch_lean(StarParams<T>& P, dim3 grid, dim3 block, bool bz, cudaStream_t stream) {
+  note_kernel("star_lean f%d R=%d axes=%d vy=%d vz=%d scale=%d bz=%d pre=%d chunk=%d grid=%ux%ux%u block=%ux%u",
+              (int)sizeof(T) * 8, R, HY ? 3 : 4, VY, VZ, P.scale_class, bz ? 1 : 0, P.lean_expr == 2 ? 1 : 0, P.x_chunk,
+              grid.x, grid.y, grid.z, block.x, block.y);
 #define FD_LEAN(SC)                                                                        \
   if (P.lean_expr == 2) {                                                                  \
     if (bz)                                                                                \

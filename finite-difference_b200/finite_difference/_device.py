@@ -87,6 +87,10 @@ class Device:
         t = torch()
         return t.zeros(int(n), dtype=t.int64, device=self.dev)
 
+    def ones_i64(self, n):
+        t = torch()
+        return t.ones(int(n), dtype=t.int64, device=self.dev)
+
     def upload(self, array, dtype, out=None):
         """Host ndarray -> device tensor (flattened, cast to ``dtype``)."""
         t = torch()

@@ -123,6 +123,30 @@ def make_slab(model):
     return Slab(dist, axis, n, axis in model.periodic)
 
 
+class RingPool:
+    """Rings whose neighbours hold mappings of them, between two models.
+
+    A ring that a peer has mapped must not go back to the allocator while the
+    peer can still store into it, and mapping it again costs two object
+    collectives plus the IPC opens.  A closed model therefore leaves such rings
+    here (``Engine.close``), keyed by their geometry, and the next model of the
+    same geometry takes them over with flag words and mappings intact
+    (``Engine.ring_pool_take``; whether every rank found one is agreed with one
+    all-reduce before the mappings are trusted).  Entries live until the process
+    ends."""
+
+    _free = {}
+
+    @classmethod
+    def take(cls, key):
+        got = cls._free.get(key)
+        return got.pop() if got else None
+
+    @classmethod
+    def give(cls, key, bundle):
+        cls._free.setdefault(key, []).append(bundle)
+
+
 class PeerLinks:
     """Peer-memory halo exchange of one field's ring (NVLink / NVSwitch box).
 
@@ -137,14 +161,20 @@ class PeerLinks:
 
     Set-up is collective (handles travel with ``all_gather_object``): every rank
     must create the links of its fields in the same order.
+
+    The flag words carry ``base + level``: a level number only grows within a
+    model, and ``retire`` moves ``base`` past everything the closed model can
+    have published, so the next model that takes the ring over (``RingPool``)
+    starts above every stale value without the words being reset.
     """
 
     TIMEOUT_NS = 20_000_000_000
     _opened = {}          # (rank, handle) -> mapped base address, per process
 
-    def __init__(self, slab, nat, ring, flags, plane_bytes, owned0, H):
+    def __init__(self, slab, nat, ring, flags, plane_bytes, owned0, H, base=0):
         import ctypes as C
         self.nat, self.H = nat, H
+        self.base = int(base)
         self.nbytes = H * plane_bytes
         self.flags = flags                     # int64[len(ring) * 2]: [slot][0: low ghost fresh, 1: high ghost fresh]
         lib = nat.lib
@@ -195,14 +225,32 @@ class PeerLinks:
         handle, off = entry[key[1]] if len(key) > 1 else entry
         got = PeerLinks._opened.get((rank, handle))
         if got is None:
+            if not PeerLinks._opened:
+                import atexit
+                atexit.register(PeerLinks.close_all, self.nat)
             base = C.c_void_p()
             self.nat.check(self.nat.lib.fd_ipc_open(handle, C.byref(base)))
             got = PeerLinks._opened[(rank, handle)] = base.value
         return got + off
 
+    def retire(self, n_levels):
+        """The model that used these links is closed (same call on every rank)."""
+        self.base += int(n_levels) + 2
+
     def push(self, k, value, stream):
         self.nat.check(self.nat.lib.fd_halo_push(self.src_lo[k], self.dst_lo[k], self.src_hi[k], self.dst_hi[k], self.nbytes,
-                                                 self.flag_lo[k], self.flag_hi[k], value, stream))
+                                                 self.flag_lo[k], self.flag_hi[k], self.base + value, stream))
 
     def wait(self, k, value, err_flags, stream):
-        self.nat.check(self.nat.lib.fd_halo_wait(self.my_lo[k], self.my_hi[k], value, self.TIMEOUT_NS, err_flags, stream))
+        self.nat.check(self.nat.lib.fd_halo_wait(self.my_lo[k], self.my_hi[k], self.base + value, self.TIMEOUT_NS,
+                                                 err_flags, stream))
+
+    @classmethod
+    def close_all(cls, nat):
+        """Unmap every neighbour buffer this process opened (process exit)."""
+        opened, cls._opened = cls._opened, {}
+        for base in opened.values():
+            try:
+                nat.lib.fd_ipc_close(base)
+            except Exception:
+                pass

@@ -55,7 +55,10 @@ class FieldState:
         self.plane = self.size // self.owned0 if self.owned0 else 0
         self.ext_shape = ((self.owned0 + 2 * self.H,) + shape[1:]) if self.H else shape
         self.ext_size = self.size + 2 * self.H * self.plane
-        self.ring = [engine.dev.empty(self.ext_size, engine.dtype) for _ in range(depth)]
+        # (several GPUs: a ring whose peer mappings survive from an earlier model of the same geometry)
+        self.pooled = engine.ring_pool_take(self, depth)
+        self.ring = (self.pooled["ring"] if self.pooled is not None
+                     else [engine.dev.empty(self.ext_size, engine.dtype) for _ in range(depth)])
         self.held = [-1] * depth          # time index each slot holds
         self.halo_ok = [False] * depth    # ghost planes of the slot are current
         self.halo_event = [None] * depth  # ... once this event (comm stream) has completed
@@ -239,6 +242,10 @@ class Engine:
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
         self.last_poll = model.time_step
         self.pending_copies = []          # [(state, slot, t, host tensor, event)]
+        self._ghost_readers = {}          # id(field) -> statements of the current step that read its ghost planes
+        self._events, self._event_next = [], 0     # transient events (recorded and waited for within one call)
+        self._halo_done = None            # comm stream: the exchange issued last has completed
+        self.closed = False
         self._box_cache = {}
         self._plans = {}                  # statement key -> launch descriptor (see _try_fused)
         self.stats = {"fused": 0, "unfused_statements": 0}
@@ -259,6 +266,65 @@ class Engine:
     def stream(self):
         return self.dev.stream_ptr
 
+    def _event(self):
+        """An event that is recorded and waited for (stream to stream) within the
+        calling function: taken round-robin from a small pool instead of being
+        created per use.  Re-recording an event does not disturb waits that were
+        issued on its earlier record."""
+        if len(self._events) < 32:
+            self._events.append(self.dev.event())
+            return self._events[-1]
+        self._event_next = (self._event_next + 1) % len(self._events)
+        return self._events[self._event_next]
+
+    def _sole_ghost_reader(self, st, t):
+        """True when at most one statement of the current step differentiates
+        level ``t`` of this field along the decomposed axis."""
+        return self._ghost_readers.get((id(st.field), t), 0) <= 1
+
+    # -------------------------------------------------- rings with peer mappings
+    def ring_pool_take(self, st, depth):
+        """A ring (with its flag words and neighbour mappings) that an earlier,
+        closed model of this process left behind for exactly this geometry."""
+        if self.slab is None or not self.peer_halo:
+            return None
+        from ._dist import RingPool
+        return RingPool.take(self._ring_key(st, depth))
+
+    def _ring_key(self, st, depth):
+        return (st.ext_size, str(self.dtype), depth, st.plane, st.owned0, st.H, self.slab.world, self.slab.rank,
+                self.slab.periodic)
+
+    def close(self):
+        """End of the model's life on the device: queued work is finished, rings
+        that neighbours have mapped go to the process-wide pool (they must not be
+        freed while a peer can still store into them, and the next model of the
+        same geometry takes them over together with the mappings)."""
+        if self.closed:
+            return
+        self.closed = True
+        try:
+            self.dev.synchronize()
+        except Exception:
+            return
+        from ._dist import RingPool
+        for st in self.states.values():
+            if st.peer:
+                st.peer.retire(self.n_t)
+                RingPool.give(self._ring_key(st, len(st.ring)),
+                              {"ring": st.ring, "flags": st.peer_flags, "links": st.peer})
+                st.peer = None
+        self.states = {}
+        self._plans.clear()
+        self._box_cache.clear()
+        self.pending_copies = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
     def wants_level(self, t):
         h = self.model.history
         if h == "last":
@@ -269,6 +335,8 @@ class Engine:
 
     # --------------------------------------------------------------- execute
     def execute(self, stmts):
+        if self.closed:
+            raise Exception("the model was closed (Model.close): it cannot be advanced any further")
         t = self.model.time_step
         if self.H is None:
             self.H = _slab_reach(stmts)
@@ -278,9 +346,15 @@ class Engine:
         for f in self.model.fields:          # initial levels go up before the first launch
             self.state(f)
         reads_new = set()
+        self._ghost_readers = readers = {}
         for _, _, node in stmts:
             if node is not None:
                 _collect_new_reads(node, t + 1, reads_new)
+                if self.H:
+                    seen = set()
+                    _collect_ghost_reads(node, seen)
+                    for key in seen:
+                        readers[key] = readers.get(key, 0) + 1
         memo = {}
         consumed = set()
         if self.fuse and self.fuse_pairs and self._try_pair(stmts, t, reads_new):
@@ -447,6 +521,7 @@ class Engine:
                 src_state.level(t + offset)
             except RuntimeError:
                 del self._plans[key]
+                self._box_cache.clear()
                 return False
             if slab:
                 src_state.refresh_ghosts(t + offset)
@@ -486,7 +561,7 @@ class Engine:
             if rim_stream is not None:
                 # the rim slabs read the same level and write disjoint points:
                 # they run beside the interior box instead of after it
-                start = self.dev.event()
+                start = self._event()
                 start.record(base)
                 rim_stream.wait_event(start)
             for i, box in enumerate(boxes):
@@ -495,7 +570,7 @@ class Engine:
                 stream = rim_stream.cuda_stream if (i and rim_stream is not None) else base_ptr
                 nat.check(launch(ref, stream))
             if rim_stream is not None:
-                done = self.dev.event()
+                done = self._event()
                 done.record(rim_stream)
                 base.wait_event(done)
 
@@ -505,7 +580,8 @@ class Engine:
             # peer-memory pushes need the statement itself to read the level-t ghosts
             # of the field it advances (see _exchange_ahead)
             own = {id(st) for st, offset, slab in sources if slab and offset == 0}
-            self._run_overlapped(run, region, pad, eager, t, {id(ls) for ls in eager if id(ls) in own and not aux})
+            self._run_overlapped(run, region, pad, eager, t,
+                                 {id(ls) for ls in eager if id(ls) in own and not aux and self._sole_ghost_reader(ls, t)})
         else:
             run(region)
         return True
@@ -528,12 +604,12 @@ class Engine:
             self._exchange_ahead(eager, t + 1, direct_ok=direct_ok)
             run(piece(inner))
             return
-        start = dev.event()
+        start = self._event()
         start.record(dev.stream)
         dev.comm_stream.wait_event(start)
         for cut in cuts:
             run(piece(cut), dev.comm_stream)
-        rims_done = dev.event()
+        rims_done = self._event()
         rims_done.record(dev.comm_stream)
         self._exchange_ahead(eager, t + 1, on_comm=True, direct_ok=direct_ok)
         run(piece(inner))
@@ -566,7 +642,7 @@ class Engine:
                 if st.peer is None and id(st) in direct_ok and len(st.ring) > 1:
                     st.peer = self._peer_links(st)
         if not on_comm:
-            ready = dev.event()
+            ready = self._event()
             ready.record(dev.stream)
         with torch.cuda.stream(dev.comm_stream):
             if not on_comm:
@@ -584,7 +660,12 @@ class Engine:
                 st.peer.wait(st.slot_index(t), t + 1, self.flags.data_ptr(), cs)
             if direct:
                 self.stats["peer_halo_exchanges"] = self.stats.get("peer_halo_exchanges", 0) + len(direct)
-            done = dev.event()
+            # one event, always recorded on the comm stream: a consumer that waits
+            # for it after a later exchange was recorded waits for that later point
+            # of the same stream, which lies behind the one it needs
+            if self._halo_done is None:
+                self._halo_done = dev.event()
+            done = self._halo_done
             done.record(dev.comm_stream)
         for st in states:
             k = st.slot_index(t)
@@ -593,11 +674,20 @@ class Engine:
 
     def _peer_links(self, st):
         """Map the neighbours' copies of this field's ring (collective); False if
-        any rank could not, in which case the field keeps isend/irecv."""
+        any rank could not, in which case the field keeps isend/irecv.  A ring
+        taken over from a closed model keeps its mappings when every rank has one."""
         from ._dist import PeerLinks
-        st.peer_flags = self.dev.zeros_i64(2 * len(st.ring))
+        pooled = st.pooled
+        st.pooled = None
+        reuse = self.slab.all_reduce(self.dev.ones_i64(1) if pooled is not None else self.dev.zeros_i64(1), "min")
+        if int(reuse.item()):
+            st.peer_flags = pooled["flags"]
+            self.stats["peer_links_reused"] = self.stats.get("peer_links_reused", 0) + 1
+            return pooled["links"]
+        st.peer_flags = pooled["flags"] if pooled is not None else self.dev.zeros_i64(2 * len(st.ring))
         self.dev.synchronize()
-        links = PeerLinks(self.slab, nat, st.ring, st.peer_flags, st.plane * self.dtype.itemsize, st.owned0, st.H)
+        links = PeerLinks(self.slab, nat, st.ring, st.peer_flags, st.plane * self.dtype.itemsize, st.owned0, st.H,
+                          base=pooled["links"].base if pooled is not None else 0)
         return links if links.ok else False
 
     def _split_boxes(self, d, region):
@@ -719,7 +809,9 @@ class Engine:
             used.add(der.axis)
             vfield, uder, c_up = got
             slab_axis = self.H and der.axis == 0
-            if not (der.periodic or slab_axis) or not (uder.periodic or slab_axis):
+            # (the ders' own flags are global facts, the same on every rank: a fixed
+            # axis needs the range predicates of the general kernels, also along the slabs)
+            if not der.periodic or not uder.periodic:
                 return False
             if slab_axis and self.H != 1:
                 return False
@@ -777,7 +869,8 @@ class Engine:
 
         eager = [st for st in [p_state] + outs if st.H and st.wants_ghosts and min(self.slab.counts) >= 3 * st.H]
         if eager and self.overlap:
-            # (the pair kernel reads the level-t ghosts of p and of the slab-axis velocity)
+            # (the pair kernel reads the level-t ghosts of p and of the slab-axis velocity,
+            # and the statements it replaces are the only ones of the step)
             self._run_overlapped(run, region, pad, eager, t, {id(st) for st in eager})
         else:
             run(region)
@@ -913,7 +1006,7 @@ class Engine:
             return
         tc = self.dev
         import torch
-        ready = tc.event()
+        ready = self._event()
         ready.record(tc.stream)
         with torch.cuda.stream(tc.copy_stream):
             tc.copy_stream.wait_event(ready)
@@ -972,6 +1065,7 @@ class Engine:
 
     def host_changed(self, field):
         self._plans.clear()
+        self._box_cache.clear()
         st = self.states.get(id(field))
         if st is not None:
             st.faces = None
@@ -1108,6 +1202,20 @@ def _slab_reach(stmts):
         if node is not None:
             walk(node)
     return reach
+
+
+def _collect_ghost_reads(node, out):
+    """(id(field), level) of every stored level that ``node`` differentiates along the decomposed axis."""
+    if isinstance(node, Der):
+        if node.slab and isinstance(node.a, Leaf):
+            out.add((id(node.a.field), node.a.t))
+        _collect_ghost_reads(node.a, out)
+    elif isinstance(node, Unary):
+        _collect_ghost_reads(node.a, out)
+    elif isinstance(node, Binary):
+        for side in (node.a, node.b):
+            if isinstance(side, Node):
+                _collect_ghost_reads(side, out)
 
 
 def _collect_new_reads(node, t_new, out):

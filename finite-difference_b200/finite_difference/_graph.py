@@ -38,6 +38,11 @@ class Leaf(Node):
         self.t = int(t)
 
     def key(self):
+        # relative to the model's time cursor, so that the same statement has the
+        # same key every step; a coefficient field (ConstantField.always) is one
+        # fixed level whatever the step
+        if self.field._is_constant:
+            return ("leaf", id(self.field), "const")
         return ("leaf", id(self.field), self.t - self.field.model.time_step)
 
 

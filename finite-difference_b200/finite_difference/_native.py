@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 FD_MAX_POINTS = 16
 FD_MAX_TERMS = 4
 FD_MAX_POST = 4
@@ -107,6 +107,7 @@ SIGNATURES = {
     "fd_abi_version": (C.c_int, []),
     "fd_last_error": (C.c_char_p, []),
     "fd_launch_count": (C.c_longlong, []),
+    "fd_last_kernel": (C.c_char_p, []),
     "fd_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_longlong)]),
     "fd_ipc_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     "fd_ipc_close": (C.c_int, [C.c_void_p]),

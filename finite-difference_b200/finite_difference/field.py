@@ -18,6 +18,7 @@ from ._history import HostHistory
 
 
 class Field:
+    _is_constant = False
 
     def __init__(self, model, name: str, edge_axes: tuple = (), n_time_ders: int = 0):
         """
@@ -328,6 +329,7 @@ prev or new properties to get the fields at the current timestep.")
 
 
 class ConstantField(Field):
+    _is_constant = True
 
     def __init__(self, model, name: str, edge_axes: tuple = ()):
         """

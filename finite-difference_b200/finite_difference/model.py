@@ -191,6 +191,20 @@ class Model:
         if self._engine is not None:
             self._engine.poll(final=True)
 
+    def close(self):
+        """Release the model's device state (additive).  ``Field.data`` is brought
+        up to date first, so results stay readable; the model cannot be advanced
+        afterwards.  On several GPUs every rank closes its model at the same point
+        of the script; buffers that neighbouring GPUs have mapped are kept for the
+        next model of the same geometry instead of being freed."""
+        if self._engine is None:
+            return
+        self.synchronize()
+        if self.history != "last":
+            for field in self.fields:
+                self._engine.sync_history(field)
+        self._engine.close()
+
 
 def _axis_problem(axis_name, vals):
     """First problem with one axis, or None (FD.py:36-58)."""

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define FD_ABI_VERSION 5
+#define FD_ABI_VERSION 6
 
 #define FD_MAX_POINTS 16 /* sample points per stencil                     */
 #define FD_MAX_TERMS 4   /* der() terms summed by one fused statement     */
@@ -94,6 +94,12 @@ const char* fd_last_error(void);
 /* Number of kernels this library has launched since load (all threads);
  * bench.py reports it as gpu_launches. */
 long long fd_launch_count(void);
+
+/* Which kernel the last fd_fused_* call of this thread launched and with what
+ * geometry, e.g. "star_lean f64 R=1 axes=3 vy=2 vz=1 chunk=8 grid=8x64x64".
+ * Diagnostic: the parity tests at the benchmark's sizes assert that they ran the
+ * launch configuration the benchmark times.  No reference counterpart. */
+const char* fd_last_kernel(void);
 
 /* ---- unfused operators (any expression DAG, any number of dimensions) ---- */
 

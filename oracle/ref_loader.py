@@ -1,9 +1,12 @@
-"""Load the UNMODIFIED reference ``FD.py`` from ``/root/reference`` (build
-container only; the GPU box does not have it).
+"""Load the UNMODIFIED reference ``FD.py``: from ``/root/reference`` in the
+build container, or from ``oracle/_ref/FD.py`` where ``__graft_entry__.build()``
+staged a copy (git-ignored, never committed; it travels to the GPU box with
+the working tree like the built ``.so``).
 
 TEST INFRASTRUCTURE ONLY.  Used by ``oracle/make_golden.py`` to generate the
-fixtures under ``tests/golden/`` and by ``tests/test_oracle.py`` to validate
-the numpy restatement against the live reference when it is present.
+fixtures under ``tests/golden/``, by ``tests/test_oracle.py`` to validate the
+numpy restatement against the live reference when it is present, and by the
+CPU legs of ``bench.py`` (``cpu_baseline``, ``--impl reference``), which time it.
 
 The reference hard-imports matplotlib, ipywidgets and numexpr (FD.py:2,4,9),
 none of which is installed here.  Empty stand-in modules are registered for
@@ -22,13 +25,32 @@ import types
 import numpy as np
 
 REFERENCE_FD = "/root/reference/src/finite_difference/FD.py"
+STAGED_FD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "FD.py")
 
 _MATH = ("exp", "abs", "sin", "cos", "tan", "arcsin", "arccos", "arctan",
          "sinh", "cosh", "tanh")
 
 
+def location():
+    """Path of the reference source to load, or None."""
+    for path in (REFERENCE_FD, STAGED_FD):
+        if os.path.isfile(path):
+            return path
+    return None
+
+
 def available() -> bool:
-    return os.path.isfile(REFERENCE_FD)
+    return location() is not None
+
+
+def stage() -> bool:
+    """Copy the reference file next to the oracle (build container only)."""
+    if not os.path.isfile(REFERENCE_FD):
+        return os.path.isfile(STAGED_FD)
+    import shutil
+    os.makedirs(os.path.dirname(STAGED_FD), exist_ok=True)
+    shutil.copyfile(REFERENCE_FD, STAGED_FD)
+    return True
 
 
 def _numexpr_stub():
@@ -50,6 +72,7 @@ def load():
         return sys.modules["_fd_reference"]
     if not available():
         raise FileNotFoundError(REFERENCE_FD)
+    path = location()
     saved = {}
     stubs = {
         "matplotlib": types.ModuleType("matplotlib"),
@@ -64,7 +87,7 @@ def load():
         saved[name] = sys.modules.get(name)
         sys.modules[name] = mod
     try:
-        spec = importlib.util.spec_from_file_location("_fd_reference", REFERENCE_FD)
+        spec = importlib.util.spec_from_file_location("_fd_reference", path)
         ref = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(ref)
     finally:

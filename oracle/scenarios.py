@@ -385,6 +385,31 @@ def edge_to_edge(fd, n=14, n_t=4, seed=13):
     return {"f": f.data, "fdot": f.dot.data, "probe": np.array(probe)}
 
 
+def cross_diffusion(fd, shape=(16, 6, 8), n_t=7, seed=17):
+    """Two fields, and the second one's statement differentiates the FIRST
+    field's current level as well: on several GPUs the ghost planes of `u` are
+    read by two statements of the same step (slabs thick enough for the
+    overlapped exchange at world sizes 2 and 4)."""
+    m = fd.Model({"t": np.arange(n_t) * 1e-2, "x": np.arange(shape[0]) * 1.0, "y": np.arange(shape[1]) * 1.0,
+                  "z": np.arange(shape[2]) * 1.0}, "t", periodic=("x", "y", "z"))
+    u = fd.Field(m, "u", n_time_ders=1)
+    c = fd.Field(m, "c", n_time_ders=1)
+    d1 = fd.Stencil([-1, 0, 1], 1)
+    d2 = fd.Stencil([-1, 0, 1], 2)
+    rng = _rng(seed)
+    _inject_ic(u, 0, rng.random(shape))
+    _inject_ic(c, 0, rng.random(shape))
+
+    def body():
+        u.dot.assign_update(0.1 * (d2.der(u.prev, "x") + d2.der(u.prev, "y") + d2.der(u.prev, "z")))
+        c.dot.assign_update(0.05 * d1.der(u.prev, "x") + 0.02 * d2.der(c.prev, "x") + 0.02 * d2.der(c.prev, "z"))
+        u.time_integrate_update()
+        c.time_integrate_update()
+
+    _loop(m, body)
+    return {"u": u.data, "c": c.data, "cdot": c.dot.data}
+
+
 def bc_conflict_prints(fd):
     """set_BC on top of set_IC prints the conflict note (FD.py:569-570)."""
     m = fd.Model({"t": range(0, 4), "x": range(0, 6)}, "t")
@@ -424,4 +449,5 @@ ALL = {
     "burgers_1d": burgers_1d,
     "edge_to_edge": edge_to_edge,
     "bc_conflict_prints": bc_conflict_prints,
+    "cross_diffusion": cross_diffusion,
 }

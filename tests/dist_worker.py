@@ -49,6 +49,30 @@ def peer_halo_case(fd, world):
     assert (m._engine.stats.get("peer_halo_exchanges", 0) >= n_t - 2) == direct, m._engine.stats
 
 
+def cross_diffusion_case(fd, world):
+    """oracle/scenarios.py:cross_diffusion on slabs: the result is the golden one
+    and only the field with a single ghost reader took the peer-memory path."""
+    from oracle import scenarios
+    from tests.scenario_check import run_and_compare
+    made = []
+    real_model = fd.Model
+
+    def spy(*a, **k):
+        made.append(real_model(*a, **k))
+        return made[-1]
+    fd.Model = spy
+    try:
+        run_and_compare("cross_diffusion", fd, check_prints=False)
+    finally:
+        fd.Model = real_model
+    eng = made[-1]._engine
+    by_name = {st.field.name: st for st in eng.states.values()}
+    if os.environ.get("FD_B200_NO_P2P", "0") != "1":
+        assert by_name["c"].peer, "c is read by its own statement only: peer-memory path expected"
+        assert not by_name["u"].peer, "u's ghosts are read by two statements: it must not be pushed"
+    assert eng.stats["unfused_statements"] == 0, eng.stats
+
+
 def main():
     backend, names = sys.argv[1], sys.argv[2:]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -68,6 +92,9 @@ def main():
         for name in names:
             if name == "__peer_halo__":
                 peer_halo_case(fd, world)
+                continue
+            if name == "__cross_diffusion__":
+                cross_diffusion_case(fd, world)
                 continue
             results = run_and_compare(name, fd, check_prints=False)
             assert results

@@ -40,7 +40,10 @@ class FakeLib:
         self.error = b""
 
     def fd_abi_version(self):
-        return 5
+        return 6
+
+    def fd_last_kernel(self):
+        return b"numpy stand-in"
 
     def fd_last_error(self):
         return self.error

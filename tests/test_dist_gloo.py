@@ -14,7 +14,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 SCENARIOS = ["heat3d_periodic", "heat3d_fixed", "heat2d_fixed", "heat2d_time_middle", "wave2d", "wave2d_5pt",
              "wave2d_fixed_nan_spread", "acoustic3d", "acoustic3d_fixed", "flux_1d", "variable_coefficient",
-             "burgers_1d", "readme_1d", "acoustic3d_wide", "acoustic2d", "heat4d_periodic", "heat1d_odd_dx"]
+             "burgers_1d", "readme_1d", "acoustic3d_wide", "acoustic2d", "heat4d_periodic", "heat1d_odd_dx",
+             "cross_diffusion"]
 
 
 def _free_port():
@@ -67,4 +68,5 @@ def test_slab_decomposition_gloo(world):
 
 
 def test_slab_decomposition_gloo_unfused():
-    launch(2, "gloo", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d"], {"FD_B200_NO_FUSE": "1"})
+    launch(2, "gloo", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d", "cross_diffusion"],
+           {"FD_B200_NO_FUSE": "1"})

@@ -26,7 +26,20 @@ def test_slab_decomposition_nccl(world):
 def test_slab_decomposition_nccl_unfused():
     if _gpus() < 2:
         pytest.skip("needs 2 GPUs")
-    launch(2, "nccl", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d"], {"FD_B200_NO_FUSE": "1"})
+    launch(2, "nccl", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d", "cross_diffusion"],
+           {"FD_B200_NO_FUSE": "1"})
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_two_statements_read_the_same_ghost_planes(world):
+    """`u`'s current level is differentiated along the slab axis by its own
+    statement and by `c`'s: a neighbour's push of level t+2 could land in the
+    slot whose level-t ghosts the second statement has yet to read, so `u` must
+    travel by isend/irecv (a rendezvous) while `c` may use peer memory.  The
+    worker checks the engine's choice and the bits."""
+    if _gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    launch(world, "nccl", ["__cross_diffusion__"])
 
 
 @pytest.mark.parametrize("world", [2, 4])

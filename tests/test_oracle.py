@@ -137,3 +137,32 @@ def test_oracle_vs_live_reference_random_der():
         ref = st.der(f.prev, "x").data
         mine = O.der(vals, pts, O.stencil_weights(pts, order), order, 1, periodic, fe, te, m.axes["x"][1] - m.axes["x"][0])
         assert _same(np.asarray(ref), mine), (pts, order, kind, periodic)
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference source not present on this machine")
+def test_port_runs_at_the_speed_of_the_live_reference():
+    """bench.py falls back to timing the numpy port where the reference file is
+    absent; this measures that the port is a fair stand-in: the same 128^3 x 3-step
+    heat run through the unmodified FD.py and through the port, best of five each,
+    within 20 % of one another (and the same bits)."""
+    import bench
+    shape = (128, 128, 128)
+    ic = np.random.default_rng(5).random(shape)
+    kind, live = bench.reference_step_fn("c3", shape)
+    assert kind == "reference"
+    saved = ref_loader.available
+    ref_loader.available = lambda: False
+    try:
+        kind, port = bench.reference_step_fn("c3", shape)
+    finally:
+        ref_loader.available = saved
+    assert kind == "port"
+    t_live, t_port = [], []
+    for _ in range(5):
+        s, state_live = live(3, (ic, None))
+        t_live.append(s)
+        s, state_port = port(3, (ic, None))
+        t_port.append(s)
+    assert np.array_equal(state_live[0], state_port[0])
+    ratio = min(t_port) / min(t_live)
+    assert 0.8 < ratio < 1.25, (t_port, t_live)
