@@ -321,6 +321,10 @@ def run_device_resident(torch, dist, fd, workload, ic, K, W, world, scaling="wea
     got["stats"] = dict(m._engine.stats)
     got["ms_local"] = got["ms"]
     got["ms"] = max_over_ranks(torch, dist, got["ms"], world)
+    if world > 1:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, round(got["ms_local"] / K, 5))
+        got["ms_per_step_by_rank"] = per_rank
     got["host_enqueue_ms"] = max_over_ranks(torch, dist, got["host_enqueue_ms"], world)
     m.close()
     del m, F, step
@@ -340,8 +344,10 @@ def workload_entry(name, got, K, world, clock, peak, points, scaling="weak"):
                           "frac_of_8TBs": achieved / 8000.0, "bytes_per_point_update": bpp,
                           "traffic": recorded_traffic(name)},
              "gpu_launches": got["launches"], "engine_stats": got["stats"]}
+    if "ms_per_step_by_rank" in got:
+        entry["ms_per_step_by_rank"] = got["ms_per_step_by_rank"]
     if clock is not None:
-        entry["clocks"] = clock.summary(got["window"])
+        entry["clocks"] = got["window"]      # resolved into a summary once the helper has delivered its samples
     return entry
 
 
@@ -498,7 +504,7 @@ def run_reference(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": desc, "grid_per_gpu": "x".join(map(str, shape)), "sample": sample, "host_threads": 1,
                    "steps_timed": timed,
-                   "code": "unmodified FD.py (oracle/_ref)" if kind == "reference" else "numpy port (oracle/fd_numpy.py)"},
+                   "code": "unmodified FD.py" if kind == "reference" else "numpy port (oracle/fd_numpy.py)"},
         "cpu_baseline": {"value": value, "unit": "point-updates/s", "cores": 1, "kind": kind, "sample": sample,
                          "host_cpus": os.cpu_count()},
         "e2e": {"value": value, "unit": "point-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -697,8 +703,10 @@ def run_b200(args):
                 "includes": "model construction, IC upload from pinned host memory, K steps, final level read back into a pinned host buffer"},
         "gpu_launches": head["launches"],
         "host_enqueue_ms_per_step": head["host_enqueue_ms"] / K,
-        "clocks": clock.summary(head["window"]),
+        "clocks": head["window"],
     }
+    if "ms_per_step_by_rank" in head:
+        line["ms_per_step_by_rank"] = head["ms_per_step_by_rank"]
     if parity is not None:
         line["parity_check"] = parity
     if others:
@@ -716,7 +724,10 @@ def run_b200(args):
                                 "sample": f"{'x'.join(map(str, sshape))} grid, 1 warm-up + 1 timed step "
                                           f"({secs:.1f} s), full numpy history like the reference",
                                 "host_cpus": os.cpu_count()}
-    clock.finish()
+    line["clocks"] = clock.summary(line["clocks"])
+    for entry in line.get("workloads", {}).values():
+        if isinstance(entry.get("clocks"), tuple):
+            entry["clocks"] = clock.summary(entry["clocks"])
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
