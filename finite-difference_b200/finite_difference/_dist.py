@@ -65,7 +65,7 @@ class Slab:
 
     # -- collectives on small host/device words ------------------------------
     def all_reduce(self, tensor, op):
-        ops = {"max": self.dist.ReduceOp.MAX, "sum": self.dist.ReduceOp.SUM}
+        ops = {"max": self.dist.ReduceOp.MAX, "sum": self.dist.ReduceOp.SUM, "min": self.dist.ReduceOp.MIN}
         self.dist.all_reduce(tensor, op=ops[op])
         return tensor
 

@@ -684,10 +684,11 @@ class Engine:
             st.peer_flags = pooled["flags"]
             self.stats["peer_links_reused"] = self.stats.get("peer_links_reused", 0) + 1
             return pooled["links"]
-        st.peer_flags = pooled["flags"] if pooled is not None else self.dev.zeros_i64(2 * len(st.ring))
+        # fresh mappings: flag words start from zero on every rank (the collectives
+        # inside PeerLinks separate this reset from the first push of any rank)
+        st.peer_flags = self.dev.zeros_i64(2 * len(st.ring))
         self.dev.synchronize()
-        links = PeerLinks(self.slab, nat, st.ring, st.peer_flags, st.plane * self.dtype.itemsize, st.owned0, st.H,
-                          base=pooled["links"].base if pooled is not None else 0)
+        links = PeerLinks(self.slab, nat, st.ring, st.peer_flags, st.plane * self.dtype.itemsize, st.owned0, st.H)
         return links if links.ok else False
 
     def _split_boxes(self, d, region):
