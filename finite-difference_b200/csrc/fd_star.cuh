@@ -350,12 +350,14 @@ static void launch_star(StarParams<T>& P, cudaStream_t stream) {
 }  // namespace fdb
 
 #include "fd_star_lean.cuh"
+#include "fd_star_row.cuh"
 
 namespace fdb {
 
 template <typename T, int R>
 void dispatch_axes(StarParams<T>& P, int axes, int mode, cudaStream_t stream) {
   if (lean_enabled() && try_star_lean<T, R>(P, axes, mode, stream)) return;
+  if (try_star_row<T, R>(P, axes, stream)) return;
 #define FD_STAR(AX)                                    \
   if (mode == 0)                                       \
     launch_star<T, R, AX, 0>(P, stream);               \

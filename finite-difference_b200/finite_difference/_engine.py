@@ -606,13 +606,18 @@ class Engine:
             return
         start = self._event()
         start.record(dev.stream)
+        # the interior is queued first: when the GPU is idle (first step after a
+        # synchronisation) it starts at once instead of after the host has issued
+        # the boundary launches and the exchange; those go to the high-priority
+        # stream and get the next free SMs.  In steady state the host runs ahead
+        # and the order of issue does not matter.
+        run(piece(inner))
         dev.comm_stream.wait_event(start)
         for cut in cuts:
             run(piece(cut), dev.comm_stream)
         rims_done = self._event()
         rims_done.record(dev.comm_stream)
         self._exchange_ahead(eager, t + 1, on_comm=True, direct_ok=direct_ok)
-        run(piece(inner))
         dev.stream.wait_event(rims_done)      # later work on the compute stream sees the whole level
 
     def _exchange_ahead(self, states, t, on_comm=False, direct_ok=()):

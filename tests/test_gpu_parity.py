@@ -402,3 +402,74 @@ def test_local_level_into_caller_buffer(fd):
     got = T.local_level(4, out=out)
     assert got is out and np.array_equal(out, want[4])
     assert np.array_equal(T.local_level(4), want[4])
+
+
+def _wave(fd, shape, n_t, periodic, ic, points, dx=1.0, dtype=np.float64):
+    names = ["x", "y"]
+    axes = {"t": np.arange(n_t) * 1e-2}
+    for n, a in zip(shape, names):
+        axes[a] = np.arange(n) * dx
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model(axes, "t", periodic=tuple(names) if periodic else (), dtype=dtype)
+        u = fd.Field(m, "u", n_time_ders=2)
+        st = fd.Stencil(list(points), 2)
+        u.set_IC_values(ic)
+        u.dot.set_IC("0")
+        while not m.finished:
+            u.dot.dot.assign_update(0.01 * (st.der(u.prev, "x") + st.der(u.prev, "y")))
+            u.dot.time_integrate_update()
+            u.time_integrate_update()
+            m.increment_time()
+    return m, u
+
+
+@pytest.mark.parametrize("shape,points,dx", [((100, 200), range(-4, 5), 1.0), ((37, 1000), range(-4, 5), 1.0),
+                                             ((130, 136), range(-3, 4), 1.0), ((64, 4096), range(-4, 5), 0.5),
+                                             ((75, 520), range(-4, 5), 0.3), ((300, 64), range(-3, 4), 1.0)])
+def test_wide_2d_wave_row_kernel(fd, shape, points, dx):
+    """Radius-3/4 stencils on 2-D periodic grids take the warp-shuffle row kernel
+    (fd_star_row.cuh): runs that do not divide into whole warps, wrapped runs,
+    every scaling class, depth-2 Euler chain, .dot.dot kept (history='all')."""
+    import finite_difference._native as nat
+    ic = np.random.default_rng(41).random(shape)
+    m, u = _wave(fd, shape, 5, True, ic, points, dx)
+    assert nat.lib.fd_last_kernel().decode().startswith("star_row f64"), nat.lib.fd_last_kernel()
+    want_u, want_v, want_a = O.run_wave(shape, 5, 0.01, 1e-2, ic, np.zeros(shape), stencil_points=tuple(points), dx=dx)
+    assert np.array_equal(u.data, want_u, equal_nan=True)
+    assert np.array_equal(u.dot.data, want_v, equal_nan=True)
+    assert np.array_equal(u.dot.dot.data, want_a, equal_nan=True)
+    assert m._engine.stats["unfused_statements"] == 0
+
+
+def test_wide_2d_wave_row_kernel_matches_general_kernel_fp32(fd):
+    """fp32 (4-element vectors, one feeding lane per side): same bits as the
+    general star kernel, which the fp32 tests pin against the float32 oracle."""
+    shape = (90, 640)
+    ic = np.random.default_rng(42).random(shape).astype(np.float32)
+    _, u = _wave(fd, shape, 4, True, ic, range(-4, 5), dtype=np.float32)
+    got = u.data
+    # (FD_B200_NO_ROW is read once per process by the library: the general kernel runs in a subprocess)
+    import subprocess
+    import sys
+    code = ("import sys, numpy as np\nsys.path[:0] = %r\nimport tests.test_gpu_parity as t, finite_difference as fd\n"
+            "ic = np.random.default_rng(42).random((90, 640)).astype(np.float32)\n"
+            "_, u = t._wave(fd, (90, 640), 4, True, ic, range(-4, 5), dtype=np.float32)\n"
+            "import finite_difference._native as nat\nassert nat.lib.fd_last_kernel().decode().startswith('star f32'), nat.lib.fd_last_kernel()\n"
+            "np.save(sys.argv[1], u.data)\n") % (sys.path[:3],)
+    import tempfile
+    with tempfile.TemporaryDirectory() as tmp:
+        out = os.path.join(tmp, "u.npy")
+        subprocess.check_call([sys.executable, "-c", code, out], env=dict(os.environ, FD_B200_NO_ROW="1"))
+        want = np.load(out)
+    assert np.array_equal(got, want, equal_nan=True)
+
+
+def test_wide_2d_heat_fixed_interior_on_row_kernel(fd):
+    """Fixed boundaries: the interior box (clean) runs the row kernel, the rim the
+    bounded general kernel; depth 1 with a 7-point stencil."""
+    shape = (150, 700)
+    ic = np.random.default_rng(43).random(shape)
+    m, T = _heat(fd, shape, 4, False, 0.05, 1e-3, ic, points=tuple(range(-3, 4)))
+    want, want_dot = O.run_heat(shape, 4, False, 0.05, 1e-3, ic, stencil_points=tuple(range(-3, 4)))
+    assert np.array_equal(T.data, want, equal_nan=True)
+    assert np.array_equal(T.dot.data, want_dot, equal_nan=True)
