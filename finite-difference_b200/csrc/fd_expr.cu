@@ -43,10 +43,10 @@ __device__ __forceinline__ float sqrt_dev<float>(float a) { return __fsqrt_rn(a)
 // One der term at one point (same code path as the scalar fused kernel).
 template <typename T>
 __device__ __forceinline__ T der_at(const DevTerm<T>& tm, int i0, int i1, int i2, bool& saw_inf) {
-  const int j = tm.axis == 0 ? i0 : (tm.axis == 1 ? i1 : i2);
+  const int j = term_index(tm, i0, i1, i2);
   if (!tm.periodic && (j < tm.lo || j >= tm.hi)) return quiet_nan<T>();
-  const int64_t base = (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2 - (int64_t)j * tm.stride[tm.axis];
-  const int64_t sa = tm.stride[tm.axis];
+  const int64_t sa = tm.sa;
+  const int64_t base = (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2 - (int64_t)j * sa;
   T acc = (T)0;
   for (int p = 0; p < tm.st.npts; ++p) {
     int jj = j + tm.st.shifts[p];

@@ -31,15 +31,14 @@ fused_kernel(const __grid_constant__ DevFused<T> P) {
     T total = (T)0;
     for (int k = 0; k < P.nterms; ++k) {
       const DevTerm<T>& tm = P.term[k];
-      const int j = tm.axis == 0 ? i0 : (tm.axis == 1 ? i1 : i2);
+      const int j = term_index(tm, i0, i1, i2);
       T d;
       if (!tm.periodic && (j < tm.lo || j >= tm.hi)) {
         d = quiet_nan<T>();
       } else {
         // offset of the source element with the axis coordinate taken out
-        const int64_t base = (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2 -
-                             (int64_t)j * tm.stride[tm.axis];
-        const int64_t sa = tm.stride[tm.axis];
+        const int64_t sa = tm.sa;
+        const int64_t base = (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2 - (int64_t)j * sa;
         T acc = (T)0;
         for (int p = 0; p < tm.st.npts; ++p) {
           int jj = j + tm.st.shifts[p];
@@ -144,13 +143,12 @@ fused_vec_kernel(const __grid_constant__ DevFused<T> P) {
           if (!tm.periodic && (i2 + e < tm.lo || i2 + e >= tm.hi)) acc[e] = quiet_nan<T>();
         }
       } else {
-        const int j = tm.axis == 0 ? i0 : i1;
-        const T* col = tm.src + (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2 -
-                       (int64_t)j * tm.stride[tm.axis];
+        const int j = term_index(tm, i0, i1, i2);
+        const T* col = tm.src + (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2 - (int64_t)j * tm.sa;
         const bool bad = !tm.periodic && (j < tm.lo || j >= tm.hi);
         for (int p = 0; p < tm.st.npts; ++p) {
           const int jj = wrap_or_clamp(j + tm.st.shifts[p], tm.n_src, tm.periodic);
-          const PK t = load_vec<T>(col + (int64_t)jj * tm.stride[tm.axis]);
+          const PK t = load_vec<T>(col + (int64_t)jj * tm.sa);
 #pragma unroll
           for (int e = 0; e < VN; ++e) acc[e] = add_rn(acc[e], mul_rn(tm.st.weights[p], t.v[e]));
         }

@@ -61,10 +61,19 @@ template <typename T>
 struct DevTerm {
   const T* src;
   int32_t axis, periodic, lo, hi, n_src, subtract, has_pre, negate;
+  int32_t fold_div, fold_mod;   // axis 0 is a merge of several leading axes (fd_term_t), fold_mod == 0: it is not
   T pre;
   int64_t stride[3];  // element strides of the source slice
+  int64_t sa;         // element stride between neighbours along the differentiated axis
   DevStencil<T> st;
 };
+
+// index of the point along the term's differentiated axis
+template <typename T>
+__device__ __forceinline__ int term_index(const DevTerm<T>& tm, int i0, int i1, int i2) {
+  if (tm.axis == 0) return tm.fold_mod ? (i0 / tm.fold_div) % tm.fold_mod : i0;
+  return tm.axis == 1 ? i1 : i2;
+}
 
 template <typename T>
 struct DevPost {
@@ -123,7 +132,18 @@ inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P, int min_terms = 1
     t.has_pre = s.has_pre;
     t.negate = s.negate;
     t.pre = (T)s.pre;
-    const int n_dst = d->n[s.axis];
+    t.fold_div = t.fold_mod = 0;
+    if (s.fold_mod != 0) {
+      if (s.axis != 0 || s.fold_mod < 1 || s.fold_div < 1 || d->n[0] % ((int64_t)s.fold_div * s.fold_mod) != 0)
+        return fail("fd_fused_step: term %d: fold (%d, %d) does not divide dimension 0 of %d points", k, s.fold_div,
+                    s.fold_mod, d->n[0]);
+      if (s.n_src != s.fold_mod) return fail("fd_fused_step: term %d: a folded axis must keep its extent", k);
+      if (s.fold_div != 1 || s.fold_mod != d->n[0]) {
+        t.fold_div = s.fold_div;
+        t.fold_mod = s.fold_mod;
+      }
+    }
+    const int n_dst = t.fold_mod ? t.fold_mod : d->n[s.axis];
     if (s.periodic) {
       if (s.n_src != n_dst) return fail("fd_fused_step: periodic term %d changes the axis length", k);
       for (int p = 0; p < t.st.npts; ++p)
@@ -140,10 +160,11 @@ inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P, int min_terms = 1
                       t.lo, t.hi, t.st.shifts[p], s.n_src);
     }
     int dims[3] = {d->n[0], d->n[1], d->n[2]};
-    dims[s.axis] = s.n_src;
+    if (!t.fold_mod) dims[s.axis] = s.n_src;
     t.stride[2] = 1;
     t.stride[1] = dims[2];
     t.stride[0] = (int64_t)dims[1] * dims[2];
+    t.sa = t.fold_mod ? t.stride[0] * t.fold_div : t.stride[s.axis];
   }
   for (int k = 0; k < FD_MAX_TERMS; ++k)
     if (k >= d->nterms) P->term[k] = P->term[0];
@@ -171,6 +192,9 @@ inline int make_dev_fused(const fd_fused_t* d, DevFused<T>* P, int min_terms = 1
         if (l < d->depth && d->face[l][a][s]) P->any_face |= (1 << a);
       }
   }
+  if (P->any_face & 1)
+    for (int k = 0; k < d->nterms; ++k)
+      if (P->term[k].fold_mod) return fail("fd_fused_step: boundary faces on dimension 0 cannot be combined with folded axes");
   P->flags = (long long*)d->flags;
   const bool no_box = d->box_hi[0] == 0 && d->box_hi[1] == 0 && d->box_hi[2] == 0 && d->box_lo[0] == 0 &&
                       d->box_lo[1] == 0 && d->box_lo[2] == 0;

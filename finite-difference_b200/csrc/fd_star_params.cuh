@@ -85,6 +85,8 @@ static bool star_applicable(const DevFused<T>& F_in, StarParams<T>* P, int* radi
     if (F.box_lo[2] % VN != 0 || (F.box_hi[2] % VN != 0 && F.box_hi[2] != F.n[2])) return false;
   }
   if (F.nterms < 1 || F.nterms > 3) return false;
+  for (int k = 0; k < F.nterms; ++k)
+    if (F.term[k].fold_mod) return false;      // more than three spatial axes: general kernels
   const DevTerm<T>& t0 = F.term[0];
   const int npts = t0.st.npts;
   if (npts < 3 || npts % 2 == 0) return false;

@@ -69,7 +69,14 @@ class FieldState:
         self.counts = engine.dev.zeros_i64(engine.n_t) if self.integrated else None
         self.counts_checked = engine.model.time_step
         s = len(field._slice_shape)
-        self.dims3 = (1,) * (3 - s) + tuple(self.ext_shape) if s <= 3 else None
+        if s <= 3:
+            self.dims3 = (1,) * (3 - s) + tuple(self.ext_shape)
+        elif not self.H:
+            # more than three spatial axes: the leading ones merge into dimension 0
+            # of the kernels' view (fd_term_t.fold_div / fold_mod)
+            self.dims3 = (int(np.prod(self.ext_shape[:-2])),) + tuple(self.ext_shape[-2:])
+        else:
+            self.dims3 = None
         if not self.constant:
             self._discover_array_faces()
         if self.constant:
@@ -422,7 +429,9 @@ class Engine:
             return None
         if node.shape != tuple(dot_field._slice_shape):
             return None
-        pad = 3 - len(dot_field._slice_shape)
+        nd = len(dot_field._slice_shape)
+        pad = 3 - nd
+        shape_nd = tuple(dot_field._slice_shape)
 
         top = nat.Expr() if program is not None else None
         d = top.base if top is not None else nat.Fused()
@@ -456,7 +465,14 @@ class Engine:
                 return None
             tm = d.term[k]
             tm.src = src.data_ptr()
-            tm.axis = der.axis + pad
+            tm.axis = max(der.axis + pad, 0)
+            tm.fold_div = tm.fold_mod = 0
+            if nd > 3 and der.axis < nd - 2:
+                # one of the merged leading axes (kept extents only: no staggered fixed axis)
+                if der.n_src != shape_nd[der.axis] or tuple(leaf.shape) != shape_nd:
+                    return None
+                tm.fold_mod = shape_nd[der.axis]
+                tm.fold_div = int(np.prod(shape_nd[der.axis + 1:nd - 2]))
             if der.slab:
                 # the slab is a non-periodic window of the global axis; ghosts hold the neighbours' planes
                 tm.periodic = 0
@@ -492,6 +508,8 @@ class Engine:
             d.prev[l] = 0 if aux else ls.level(t).data_ptr()      # 0: level 0 is the assigned field itself
             d.out[l] = ls.ring[ls.slot_index(t + 1)].data_ptr()
             for (dim, side), (_, per_time) in ls.face_items():
+                if nd > 3 and dim < nd - 2:
+                    return None          # a boundary face across merged axes has no place in the 3-D view
                 d.face[l][dim + pad][side] = ls.face_ptr(dim, side, t + 1)
                 if per_time:
                     dyn_faces.append((l, dim + pad, side, ls, dim))
@@ -703,7 +721,7 @@ class Engine:
         boundary face applies, so the kernel runs its predicate-free
         instantiation there; the thin rim slabs take the bounded one.  Every
         point is still computed exactly once, in one pass."""
-        if not self.split_rim:
+        if not self.split_rim or any(d.term[k].fold_mod for k in range(d.nterms)):
             return [region]
         inner = [list(r) for r in region]
         for k in range(d.nterms):
@@ -776,7 +794,7 @@ class Engine:
         p_state = self.state(p_field)
         dims3 = p_state.dims3
         vn = 16 // self.dtype.itemsize
-        if dims3 is None or dims3[2] % vn or dims3[2] < 3 * vn:
+        if dims3 is None or dims3[2] % vn or dims3[2] < 3 * vn or len(p_field._slice_shape) > 3:
             return False
         shape = tuple(p_field._slice_shape)
         pad = 3 - len(shape)

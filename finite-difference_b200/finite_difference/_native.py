@@ -44,6 +44,7 @@ class Term(C.Structure):
                 ("lo", C.c_int32), ("hi", C.c_int32),
                 ("n_src", C.c_int32), ("subtract", C.c_int32),
                 ("has_pre", C.c_int32), ("negate", C.c_int32),
+                ("fold_div", C.c_int32), ("fold_mod", C.c_int32),
                 ("pre", C.c_double),
                 ("st", Stencil)]
 

@@ -153,13 +153,22 @@ int fd_count_nan_f32(const void* src, int64_t n, void* nan_count, void* stream);
  * by one). */
 typedef struct fd_term {
   const void* src;
-  int32_t axis;      /* 0,1,2 in the collapsed (n0,n1,n2) view, n2 contiguous */
+  int32_t axis;      /* 0,1,2 in the collapsed (n0,n1,n2) view, n2 contiguous
+                        (fewer than three spatial axes: leading extents are 1) */
   int32_t periodic;
   int32_t lo, hi;    /* computed output range along axis when not periodic    */
   int32_t n_src;
   int32_t subtract;  /* 0: sum += term, 1: sum -= term (first term: ignored)   */
   int32_t has_pre;   /* multiply the term by `pre` before summing (k*der(..))  */
   int32_t negate;    /* unary minus on the term before summing                 */
+  /* More than three spatial axes (FD.py:1007-1012 applies der to any axis of an
+   * N-D array): dimension 0 of the collapsed view is then the row-major merge of
+   * all leading axes, and a term along one of THEM sets axis = 0, fold_mod = that
+   * axis' extent and fold_div = the product of the extents of the merged axes
+   * behind it; its index along the axis is (i0 / fold_div) % fold_mod.  The
+   * source must have the target's extents (n_src == fold_mod) and no boundary
+   * face may lie on dimension 0.  fold_mod == 0: dimension 0 is one axis. */
+  int32_t fold_div, fold_mod;
   double pre;
   fd_stencil_t st;
 } fd_term_t;

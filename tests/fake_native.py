@@ -134,6 +134,19 @@ class FakeLib:
         return 0
 
     # -- fused --------------------------------------------------------------
+    def _term(self, tm, n, flags):
+        """One der term of a fused descriptor on the whole (n0, n1, n2) view."""
+        shifts, weights, scale = self._stencil(tm.st)
+        if tm.fold_mod and not (tm.fold_div == 1 and tm.fold_mod == n[0]):
+            # dimension 0 merges several leading axes; differentiate the folded one
+            view = (n[0] // (tm.fold_div * tm.fold_mod), tm.fold_mod, tm.fold_div, n[1], n[2])
+            src = _arr(tm.src, int(np.prod(n))).reshape(view)
+            return self._der(src, 1, shifts, weights, scale, tm.periodic, tm.lo, tm.hi, tm.fold_mod, flags).reshape(n)
+        sshape = list(n)
+        sshape[tm.axis] = tm.n_src
+        src = _arr(tm.src, int(np.prod(sshape))).reshape(sshape)
+        return self._der(src, tm.axis, shifts, weights, scale, tm.periodic, tm.lo, tm.hi, n[tm.axis], flags)
+
     def fd_fused_step_f64(self, desc, stream):
         self.launches += 1
         d = desc._obj if hasattr(desc, "_obj") else desc.contents
@@ -143,11 +156,7 @@ class FakeLib:
         total = None
         for k in range(d.nterms):
             tm = d.term[k]
-            shifts, weights, scale = self._stencil(tm.st)
-            sshape = list(n)
-            sshape[tm.axis] = tm.n_src
-            src = _arr(tm.src, int(np.prod(sshape))).reshape(sshape)
-            v = self._der(src, tm.axis, shifts, weights, scale, tm.periodic, tm.lo, tm.hi, n[tm.axis], flags)
+            v = self._term(tm, n, flags)
             if tm.negate:
                 v = -v
             if tm.has_pre:
@@ -254,12 +263,7 @@ def _expr(self, desc, stream):
         for pc in range(x.ncode):
             op, arg, imm = x.op[pc], x.arg[pc], x.imm[pc]
             if op == 0:
-                tm = d.term[arg]
-                shifts, weights, scale = self._stencil(tm.st)
-                sshape = list(n)
-                sshape[tm.axis] = tm.n_src
-                src = _arr(tm.src, int(np.prod(sshape))).reshape(sshape)
-                stack.append(self._der(src, tm.axis, shifts, weights, scale, tm.periodic, tm.lo, tm.hi, n[tm.axis], flags))
+                stack.append(self._term(d.term[arg], n, flags))
             elif op == 1:
                 stack.append(np.array(_arr(x.field[arg], size).reshape(n)))
             elif op == 2:
@@ -288,7 +292,7 @@ def _expr(self, desc, stream):
         _arr(d.dot_out, size).reshape(n)[region] = total[region]
     rate = total
     for l in range(d.depth):
-        new = _arr(d.prev[l], size).reshape(n) + rate * d.dt
+        new = _arr(d.prev[l], size).reshape(n) + rate * d.dt if d.prev[l] else np.array(rate, dtype=float)
         stored = np.full(n, np.nan)
         for dim in range(3):
             for side in range(2):

@@ -473,3 +473,16 @@ def test_wide_2d_heat_fixed_interior_on_row_kernel(fd):
     want, want_dot = O.run_heat(shape, 4, False, 0.05, 1e-3, ic, stencil_points=tuple(range(-3, 4)))
     assert np.array_equal(T.data, want, equal_nan=True)
     assert np.array_equal(T.dot.data, want_dot, equal_nan=True)
+
+
+def test_more_than_three_spatial_axes_fused(fd):
+    """4-, 5- and 6-D grids: the leading axes merge into dimension 0 of the
+    kernels' view and a der along one of them carries its fold; one launch per
+    statement, the oracle's bits.  (Fixed boundaries on merged axes keep the
+    unfused operators.)"""
+    from tests.nd_cases import CASES, run_case
+    for shape, periodic, n_ders in CASES:
+        got, want, stats = run_case(fd, shape, periodic, n_ders)
+        assert np.array_equal(got, want, equal_nan=True), (shape, periodic)
+        if periodic:
+            assert stats["fused"] == 3 and stats["unfused_statements"] == 0, (shape, stats)

@@ -257,3 +257,39 @@ def test_auxiliary_assign_is_fused():
     finally:
         M.Model._get_engine = orig
     assert engines and all(e.stats["unfused_statements"] == 0 and e.stats["fused"] == 10 for e in engines)
+
+
+def test_more_than_three_spatial_axes_host_planner():
+    """CPU twin of the GPU test of the same name: the planner folds the leading
+    axes and hands the stand-in the same descriptors the kernels get."""
+    import numpy as np
+    from tests.nd_cases import CASES, run_case
+    with fake_native.installed():
+        for shape, periodic, n_ders in CASES:
+            got, want, stats = run_case(fd, shape, periodic, n_ders)
+            assert np.array_equal(got, want, equal_nan=True), (shape, periodic)
+            if periodic:
+                assert stats["fused"] == 3 and stats["unfused_statements"] == 0, (shape, stats)
+
+
+def test_constant_field_leaf_keeps_its_plan():
+    """A coefficient field (ConstantField.always) is one fixed level: the plan of
+    a statement that uses it is found again every step instead of being rebuilt."""
+    import contextlib
+    import io
+    import numpy as np
+    with fake_native.installed():
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model({"t": np.arange(9) * 1e-2, "x": np.arange(10) * 1.0, "y": np.arange(8) * 1.0}, "t",
+                         periodic=("x", "y"))
+            T = fd.Field(m, "T", n_time_ders=1)
+            kappa = fd.ConstantField(m, "kappa")
+            kappa.set("1+x*y/50")
+            d2 = fd.Stencil([-1, 0, 1], 2)
+            T.set_IC("x+y")
+            while not m.finished:
+                T.dot.assign_update(kappa.always * (d2.der(T.prev, "x") + d2.der(T.prev, "y")))
+                T.time_integrate_update()
+                m.increment_time()
+        assert m._engine.stats["fused"] == 8
+        assert len(m._engine._plans) == 2          # one per ring parity
