@@ -223,6 +223,60 @@ class FieldState:
         return self.faces.items()
 
 
+class _TempField:
+    """Stands where a Field would for the value of an inner expression of a nested
+    ``der`` (``d.der(kappa.always * d.der(T.prev, "x"), "x")``): one scratch level,
+    no history, no boundary faces."""
+    _is_constant = False
+    _bc_locations = ()
+    _parent = None
+    dot = None
+
+    def __init__(self, model, shape, name):
+        self.model, self._slice_shape, self.name = model, tuple(shape), name
+        self._temp_state = None
+
+
+class TempState:
+    """Device side of a _TempField: what the plan builder asks of a FieldState."""
+    constant = integrated = wants_ghosts = False
+    counts = peer = pooled = None
+    H = 0
+
+    def __init__(self, engine, field):
+        self.field, self.engine = field, engine
+        shape = tuple(field._slice_shape)
+        self.size = self.ext_size = int(np.prod(shape)) if shape else 1
+        self.owned0 = shape[0] if shape else 1
+        self.plane = self.size // self.owned0 if self.owned0 else 0
+        self.ext_shape = shape
+        self.ring = [engine.dev.empty(self.size, engine.dtype)]
+        s = len(shape)
+        self.dims3 = (1,) * (3 - s) + shape if s <= 3 else (int(np.prod(shape[:-2])),) + shape[-2:]
+
+    def slot_index(self, t):
+        return 0
+
+    def level(self, t):
+        return self.ring[0]
+
+    claim = level
+
+    def refresh_ghosts(self, t):
+        pass
+
+    def face_items(self):
+        return ()
+
+    def face_ptr(self, dim, side, t):
+        return 0
+
+
+class TempLeaf(Leaf):
+    """The scratch level of an inner expression, as a source of der terms."""
+    __slots__ = ()
+
+
 class Engine:
     def __init__(self, model):
         self.model = model
@@ -241,6 +295,7 @@ class Engine:
         self.fuse_expr = os.environ.get("FD_B200_NO_EXPR", "0") != "1"
         self.rims_beside = os.environ.get("FD_B200_NO_SIDE_RIMS", "0") != "1"
         self.fuse_aux = os.environ.get("FD_B200_NO_AUX", "0") != "1"
+        self.fuse_nested = os.environ.get("FD_B200_NO_NESTED", "0") != "1"
         # halo planes written straight into the neighbours' memory (one NVLink box, NCCL ranks)
         self.peer_halo = (os.environ.get("FD_B200_NO_P2P", "0") != "1" and self.slab is not None
                           and self.slab.backend == "nccl" and self.dev.comm_stream is not None)
@@ -258,10 +313,13 @@ class Engine:
         self.stats = {"fused": 0, "unfused_statements": 0}
         self._fn = {name: nat.fn(name, self.dtype) for name in
                     ("fd_der", "fd_ewise", "fd_merge_store", "fd_fill", "fd_face_store", "fd_count_nan",
-                     "fd_fused_step", "fd_fused_pair", "fd_fused_expr")}
+                     "fd_fused_step", "fd_fused_pair", "fd_fused_expr", "fd_fused_nested")}
 
     # ------------------------------------------------------------------ utils
     def state(self, field):
+        temp = getattr(field, "_temp_state", None)
+        if temp is not None:
+            return temp
         st = self.states.get(id(field))
         if st is None:
             if self.H is None:
@@ -406,6 +464,19 @@ class Engine:
     def _build_fused_plan(self, dot_field, node, chain, t):
         """Match the statement and fill the launch descriptor for the ring parity of
         step ``t``; returns None when the statement needs the unfused operators."""
+        # a der of a computed expression: the inner expression gets a scratch level of
+        # its own (one plain-assignment launch), the statement then reads that level
+        inner_plans = []
+        if _has_nested_der(node):
+            if self.H or not self.fuse_nested:
+                return None
+            node, lifted = _lift_nested_ders(node, self.model, t)
+            for leaf, inner in lifted:
+                leaf.field._temp_state = TempState(self, leaf.field)
+                plan = self._build_fused_plan(leaf.field, inner, [], t)
+                if plan is None:
+                    return None
+                inner_plans.append(plan)
         dot_state = self.state(dot_field)
         dims3 = dot_state.dims3
         # no chain: the assign_update alone (an auxiliary field such as a flux, or a
@@ -518,7 +589,42 @@ class Engine:
             d.rim_lo[a], d.rim_hi[a] = 0, max(dims3[a] - 1, 0)
         if self.H:
             d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
-        return d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux
+        for ip in inner_plans:
+            sources += ip[3]
+        nested = None
+        if len(inner_plans) == 1 and not inner_plans[0][9]:
+            # the usual case, one inner expression: both launches go through
+            # fd_fused_nested, which fills the scratch level in where the
+            # descriptors say NULL
+            ip = inner_plans[0]
+            scratch = ip[1].ring[0]
+            inner_d = ip[0]
+            inner_d.out[0] = 0
+            hits = 0
+            for k in range(d.nterms):
+                if d.term[k].src == scratch.data_ptr():
+                    d.term[k].src = 0
+                    hits += 1
+            if top is not None:
+                for j in range(top.nfields):
+                    if top.field[j] == scratch.data_ptr():
+                        top.field[j] = 0
+                        hits += 1
+            if hits:
+                nested = (1 if ip[7] is not None else 0, ip[7] if ip[7] is not None else inner_d, scratch)
+        return d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux, inner_plans, nested
+
+    def _launch_inner(self, plan):
+        """The scratch level of an inner expression (plain assignment, whole level)."""
+        d, _, _, _, _, _, dims3, top, _, inners, _ = plan
+        for ip in inners:
+            self._launch_inner(ip)
+        for a in range(3):
+            d.box_lo[a], d.box_hi[a] = 0, dims3[a]
+        if top is None:
+            nat.check(self._fn["fd_fused_step"](C.byref(d), self.stream))
+        else:
+            nat.check(self._fn["fd_fused_expr"](C.byref(top), self.stream))
 
     def _try_fused(self, dot_field, node, chain, t, reads_new):
         # the same statement comes back every step: its launch descriptor is
@@ -533,7 +639,7 @@ class Engine:
                 self._plans.clear()
                 self._box_cache.clear()
             self._plans[key] = plan
-        d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux = plan
+        d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux, inner_plans, nested = plan
         for src_state, offset, slab in sources:
             try:
                 src_state.level(t + offset)
@@ -566,6 +672,20 @@ class Engine:
         ref = C.byref(d if top is None else top)
         if top is not None:
             self.stats["fused_expr"] = self.stats.get("fused_expr", 0) + 1
+        if inner_plans:
+            self.stats["fused_nested"] = self.stats.get("fused_nested", 0) + 1
+            for a in range(3):
+                d.box_lo[a], d.box_hi[a] = region[a]
+            if nested is not None:
+                inner_is_expr, inner_desc, scratch = nested
+                nat.check(self._fn["fd_fused_nested"](inner_is_expr, C.addressof(inner_desc), 0 if top is None else 1,
+                                                      C.addressof(d if top is None else top), scratch.data_ptr(),
+                                                      scratch.numel(), self.stream))
+            else:
+                for ip in inner_plans:
+                    self._launch_inner(ip)
+                nat.check(launch(ref, self.stream))
+            return True
 
         def run(piece, on=None):
             base = on if on is not None else self.dev.stream        # None on the CPU stand-in
@@ -1203,6 +1323,48 @@ def _compile_expr(node):
             or len(code) > nat.FD_EXPR_MAX_CODE or depth[1] > nat.FD_EXPR_MAX_STACK):
         return None
     return ders, leaves, code
+
+
+def _has_nested_der(node):
+    if isinstance(node, Der):
+        return not isinstance(node.a, Leaf) or _has_nested_der(node.a)
+    if isinstance(node, Unary):
+        return _has_nested_der(node.a)
+    if isinstance(node, Binary):
+        return any(isinstance(s, Node) and _has_nested_der(s) for s in (node.a, node.b))
+    return False
+
+
+def _lift_nested_ders(node, model, t):
+    """Replace the argument of every der that is not a stored level by a scratch
+    leaf.  Returns (rewritten tree, [(scratch leaf, inner expression)]); equal
+    inner expressions share one scratch level.  (Ders nested deeper stay inside
+    the inner expressions: they are lifted when those get their own plans.)"""
+    lifted, by_key = [], {}
+
+    def walk(n):
+        if isinstance(n, Der):
+            if isinstance(n.a, Leaf):
+                return n
+            key = n.a.key()
+            leaf = by_key.get(key)
+            if leaf is None:
+                leaf = by_key[key] = TempLeaf(_TempField(model, n.a.shape, f"scratch {len(lifted)}"), t)
+                lifted.append((leaf, n.a))
+            new = Der(leaf, n.shape, n.axis, n.shifts, n.weights, n.scale, n.periodic, n.lo, n.hi, n.n_src, n.n_dst,
+                      n.stencil)
+            new.slab = n.slab
+            return new
+        if isinstance(n, Unary):
+            a = walk(n.a)
+            return n if a is n.a else Unary(n.op, a)
+        if isinstance(n, Binary):
+            a = walk(n.a) if isinstance(n.a, Node) else n.a
+            b = walk(n.b) if isinstance(n.b, Node) else n.b
+            return n if (a is n.a and b is n.b) else Binary(n.op, a, b)
+        return n
+
+    return walk(node), lifted
 
 
 def _slab_reach(stmts):

@@ -127,6 +127,7 @@ for _sfx in ("f64", "f32"):
         f"fd_fused_step_{_sfx}": (_I, [C.POINTER(Fused), _P]),
         f"fd_fused_pair_{_sfx}": (_I, [C.POINTER(Pair), _P]),
         f"fd_fused_expr_{_sfx}": (_I, [C.POINTER(Expr), _P]),
+        f"fd_fused_nested_{_sfx}": (_I, [_I, _P, _I, _P, _P, C.c_longlong, _P]),
     })
 
 

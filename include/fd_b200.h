@@ -312,6 +312,25 @@ typedef struct fd_expr {
 int fd_fused_expr_f64(const fd_expr_t* desc, void* stream);
 int fd_fused_expr_f32(const fd_expr_t* desc, void* stream);
 
+/* ---- a derivative of a computed expression -------------------------------- */
+
+/* Stencil.der accepts any FieldInstant (FD.py:990-1003), e.g.
+ *     T.dot.assign_update(d.der(kappa.always * d.der(T.prev, "x"), "x"))
+ *     u.dot.assign_update(-0.5 * d.der(u.prev * u.prev, "x"))
+ * In the reference the inner expression is an array of its own.  Here it is
+ * evaluated ONCE into a scratch level by a plain-assignment launch (`inner`:
+ * depth 1, prev[0] == NULL, out[0] == NULL = "the scratch level"), and the
+ * statement proper (`outer`) then reads the scratch level wherever it names a
+ * NULL source (term[k].src, and field[k] of an fd_expr_t): two launches instead
+ * of one per reference array operation, the same values bit for bit.
+ * inner_is_expr / outer_is_expr: the descriptor is an fd_expr_t (1) or an
+ * fd_fused_t (0).  `scratch` holds scratch_elems values of the entry point's
+ * type; the inner expression must fit (n[0]*n[1]*n[2] values). */
+int fd_fused_nested_f64(int inner_is_expr, const void* inner, int outer_is_expr, const void* outer, void* scratch,
+                        long long scratch_elems, void* stream);
+int fd_fused_nested_f32(int inner_is_expr, const void* inner, int outer_is_expr, const void* outer, void* scratch,
+                        long long scratch_elems, void* stream);
+
 /* ---- halo exchange over peer memory (multi-GPU slabs) --------------------
  *
  * No reference counterpart: the reference is a single-process numpy program.

@@ -410,6 +410,66 @@ def cross_diffusion(fd, shape=(16, 6, 8), n_t=7, seed=17):
     return {"u": u.data, "c": c.data, "cdot": c.dot.data}
 
 
+def nested_divgrad(fd, n_t=5):
+    """der of a computed expression, twice: div(kappa grad T) written with
+    first-derivative stencils (FD.py:990-1003 accepts any FieldInstant)."""
+    m = fd.Model({"t": np.arange(n_t) * 1e-2, "x": np.arange(12) * 1.0, "y": np.arange(16) * 0.5}, "t",
+                 periodic=("x", "y"))
+    T = fd.Field(m, "T", n_time_ders=1)
+    kappa = fd.ConstantField(m, "kappa")
+    kappa.set("1+x*y/50")
+    d1 = fd.Stencil([-1, 0, 1], 1)
+    T.set_IC("x*x+y")
+
+    def body():
+        T.dot.assign_update(d1.der(kappa.always * d1.der(T.prev, "x"), "x")
+                            + d1.der(kappa.always * d1.der(T.prev, "y"), "y"))
+        T.time_integrate_update()
+
+    _loop(m, body)
+    return {"T": T.data, "Tdot": T.dot.data}
+
+
+def nested_burgers(fd, n_t=5):
+    """Conservative Burgers flux: der of a product of stored levels, fixed axis
+    with boundary values (the inner array has no NaN, the der of it does)."""
+    m = fd.Model({"t": np.arange(n_t) * 1e-2, "x": np.arange(40) * 0.5}, "t")
+    u = fd.Field(m, "u", n_time_ders=1)
+    d1 = fd.Stencil([-1, 0, 1], 1)
+    d2 = fd.Stencil([-1, 0, 1], 2)
+    u.set_IC("1+x/40")
+    u.set_BC("1", "x", "start")
+    u.set_BC("1.5", "x", "end")
+
+    def body():
+        u.dot.assign_update(-0.5 * d1.der(u.prev * u.prev, "x") + 0.05 * d2.der(u.prev, "x"))
+        u.time_integrate_update()
+
+    _loop(m, body)
+    return {"u": u.data, "udot": u.dot.data}
+
+
+def nested_staggered_flux(fd, n_t=5):
+    """edge->cell der of (a factor times a cell->edge der): the flux form of
+    diffusion without an auxiliary field; the inner array lives on the edges of a
+    fixed axis (one more point than the field)."""
+    m = fd.Model({"t": np.arange(n_t) * 1e-2, "x": np.arange(20) * 1.0, "y": np.arange(8) * 1.0}, "t",
+                 periodic=("y",))
+    T = fd.Field(m, "T", n_time_ders=1)
+    ce = fd.Stencil([-.5, .5], 1, "cell", "edge")
+    ec = fd.Stencil([-.5, .5], 1, "edge", "cell")
+    T.set_IC("x+y*y")
+    T.set_BC("0", "x", "start")
+    T.set_BC("3", "x", "end")
+
+    def body():
+        T.dot.assign_update(ec.der(0.3 * ce.der(T.prev, "x"), "x"))
+        T.time_integrate_update()
+
+    _loop(m, body)
+    return {"T": T.data, "Tdot": T.dot.data}
+
+
 def bc_conflict_prints(fd):
     """set_BC on top of set_IC prints the conflict note (FD.py:569-570)."""
     m = fd.Model({"t": range(0, 4), "x": range(0, 6)}, "t")
@@ -450,4 +510,7 @@ ALL = {
     "edge_to_edge": edge_to_edge,
     "bc_conflict_prints": bc_conflict_prints,
     "cross_diffusion": cross_diffusion,
+    "nested_divgrad": nested_divgrad,
+    "nested_burgers": nested_burgers,
+    "nested_staggered_flux": nested_staggered_flux,
 }

@@ -320,6 +320,41 @@ def _expr(self, desc, stream):
 FakeLib.fd_fused_expr_f64 = _expr
 
 
+def _nested(self, inner_is_expr, inner, outer_is_expr, outer, scratch, scratch_elems, stream):
+    """fd_fused_nested_f64: the scratch level goes where the descriptors say NULL."""
+    import finite_difference._native as nat
+
+    class _Ref:                      # what the fakes expect from a byref()
+        def __init__(self, obj):
+            self._obj = obj
+
+    def copy(kind, address):
+        cls = nat.Expr if kind else nat.Fused
+        return cls.from_buffer_copy(cls.from_address(int(address)))
+
+    i, o = copy(inner_is_expr, inner), copy(outer_is_expr, outer)
+    ib, ob = (i.base if inner_is_expr else i), (o.base if outer_is_expr else o)
+    assert ib.depth == 1 and not ib.prev[0] and not ib.out[0] and not ib.dot_out
+    assert ib.n[0] * ib.n[1] * ib.n[2] <= scratch_elems
+    ib.out[0] = scratch
+    hits = 0
+    for k in range(ob.nterms):
+        if not ob.term[k].src:
+            ob.term[k].src = scratch
+            hits += 1
+    if outer_is_expr:
+        for k in range(o.nfields):
+            if not o.field[k]:
+                o.field[k] = scratch
+                hits += 1
+    assert hits
+    rc = (self.fd_fused_expr_f64 if inner_is_expr else self.fd_fused_step_f64)(_Ref(i), stream)
+    return rc or (self.fd_fused_expr_f64 if outer_is_expr else self.fd_fused_step_f64)(_Ref(o), stream)
+
+
+FakeLib.fd_fused_nested_f64 = _nested
+
+
 class FakeDevice:
     index = 0
 

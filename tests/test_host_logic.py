@@ -293,3 +293,24 @@ def test_constant_field_leaf_keeps_its_plan():
                 m.increment_time()
         assert m._engine.stats["fused"] == 8
         assert len(m._engine._plans) == 2          # one per ring parity
+
+
+@pytest.mark.parametrize("name,launches", [("nested_burgers", 2), ("nested_staggered_flux", 2), ("nested_divgrad", 3)])
+def test_der_of_a_computed_expression_is_fused(name, launches):
+    """One scratch level per inner expression plus the statement itself: 2 (or
+    3) launches per step instead of one per reference array operation."""
+    made = []
+    real = fd.Model
+
+    def spy(*a, **k):
+        made.append(real(*a, **k))
+        return made[-1]
+    with fake_native.installed() as lib:
+        fd.Model = spy
+        try:
+            run_and_compare(name, fd, check_prints=False)
+        finally:
+            fd.Model = real
+        stats = made[-1]._engine.stats
+        assert stats["unfused_statements"] == 0 and stats["fused_nested"] == 4, stats
+        assert lib.launches - 4 * launches in (1, 2), lib.launches   # + NaN count (and device fill) of the initial level
