@@ -14,8 +14,9 @@
 //     the neighbouring lanes*: warp shuffles, no load at all.  The HL outermost
 //     lanes on either side of the run only feed their neighbours (their own
 //     results are not stored), so consecutive warps overlap by 2*HL vectors;
-//   * every global load of an iteration (the prefetched row, the next row of the
-//     other integrated level) is issued one iteration before it is consumed.
+//   * the row entering the window and the row of the other integrated level are
+//     copied to shared memory asynchronously several rows ahead (cp.async, one
+//     private 16-byte slot per lane and row: no barrier).
 // Arithmetic is the reference's, operation for operation (FD.py:1054-1055,
 // 1107-1110, 515-516), as in star_kernel.
 #pragma once
@@ -39,20 +40,39 @@ __device__ __forceinline__ T row_scale(T v, const StarAxis<T>& a) {
   return div_invariant(v, a.scale, a.inv);
 }
 
+// ---- asynchronous staging: every lane copies the 16 bytes it will need kRowAhead
+// rows later straight into its own slot of shared memory (cp.async), so that the
+// bytes in flight per SM do not depend on the register budget (one row ahead in
+// registers kept 16 KB per SM in flight and ran at 0.66 of the HBM peak with long-
+// scoreboard stalls; the B200 needs about three times that).  A lane only ever
+// reads back what it copied itself: no barrier, cp.async.wait_group alone.
+constexpr int kRowAhead = 4;
+
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // 4 warps per block, each an independent run; blockIdx.y = chunk of marched rows
 template <typename T, int R, int DEPTH, int SCALE>
-__global__ void __launch_bounds__(128, sizeof(T) == 8 ? 4 : 5)
+__global__ void __launch_bounds__(128, sizeof(T) == 8 ? 5 : 6)
 star_row_kernel(const __grid_constant__ StarParams<T> P) {
   constexpr int VN = Vec<T>::N;
-  constexpr int NP = 2 * R + 1;
-  constexpr int NW = NP + 1;                   // rows in the register window: 2R+1 in use, one prefetched
+  constexpr int NP = 2 * R + 1;                // rows in the register window
   constexpr int HL = (R + VN - 1) / VN;        // feeding lanes on either side of a run
   constexpr int OUTL = 32 - 2 * HL;            // lanes whose results are stored
+  constexpr int D = kRowAhead, SLOTS = D + 1;  // D copies in flight, one slot being read
   using PK = Pack<T, VN>;
+  __shared__ __align__(16) PK stage[SLOTS][1 + DEPTH][128];   // [slot][0: differentiated level, 1+l: prev[l]][thread]
   const DevFused<T>& F = P.F;
   const int n0 = F.n[0], n2 = F.n[2];          // marched rows, contiguous extent (F.n[1] == 1)
   const int nvec = n2 / VN;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int seg = blockIdx.x * 4 + warp;
   const int v_out0 = F.box_lo[2] / VN + seg * OUTL;    // first vector this warp stores
   if (v_out0 >= F.box_hi[2] / VN) return;               // (whole warp)
@@ -69,33 +89,41 @@ star_row_kernel(const __grid_constant__ StarParams<T> P) {
   unsigned nan_cnt[2] = {0u, 0u};
   bool saw_inf = false;
 
-  PK win[NW];
+  // what iteration j (row x_begin + j) needs beyond the rows already in the
+  // window: the row R ahead of it, and its own row of the other integrated levels
+  auto stage_rows = [&](const int j) {
+    const int x = x_begin + j;
+    if (x < x_end) {
+      const int slot = j % SLOTS;
+      cp_async_16(&stage[slot][0][tid], col + (int64_t)wrap_or_clamp(x + R, n0, ax.periodic) * n2);
 #pragma unroll
-  for (int p = 0; p < NP; ++p) win[p] = load_vec<T>(col + (int64_t)wrap_or_clamp(x_begin - R + p, n0, ax.periodic) * n2);
+      for (int l = 0; l < DEPTH; ++l)
+        if (!P.prev_is_src[l] && is_out) cp_async_16(&stage[slot][1 + l][tid], F.prev[l] + (int64_t)x * n2 + col_off);
+    }
+    cp_async_commit();      // (possibly empty: the group count stays in step with the iterations)
+  };
+#pragma unroll
+  for (int j = 0; j < D; ++j) stage_rows(j);
 
-  // levels of the Euler chain that are not the differentiated level itself are
-  // read one row ahead (only by the lanes that store)
-  PK ahead[DEPTH];
+  PK win[NP];               // rows x-R .. x+R; the last one arrives through shared memory
 #pragma unroll
-  for (int l = 0; l < DEPTH; ++l) {
-#pragma unroll
-    for (int e = 0; e < VN; ++e) ahead[l].v[e] = (T)0;
-    if (!P.prev_is_src[l] && is_out) ahead[l] = load_vec<T>(F.prev[l] + (int64_t)x_begin * n2 + col_off);
-  }
+  for (int p = 0; p < NP - 1; ++p) win[p] = load_vec<T>(col + (int64_t)wrap_or_clamp(x_begin - R + p, n0, ax.periodic) * n2);
 
   int64_t row_off = (int64_t)x_begin * n2 + col_off;
-  // one marched row; `u` is the position of the iteration within a group of NW:
+  int slot = 0;
+  // one marched row; `u` is the position of the iteration within a group of NP:
   // the window rotates by index arithmetic that is static once the group is
   // unrolled, instead of by moving 2R+1 vectors from register to register
   auto body = [&](const int u, const int x) {
-    win[(NP + u) % NW] = load_vec<T>(col + (int64_t)wrap_or_clamp(x + R + 1, n0, ax.periodic) * n2);
+    cp_async_wait<D - 1>();                     // the copies issued for this iteration have landed
+    win[(NP - 1 + u) % NP] = stage[slot][0][tid];
     PK cur[DEPTH];
 #pragma unroll
-    for (int l = 0; l < DEPTH; ++l) {
-      cur[l] = ahead[l];
-      if (!P.prev_is_src[l] && is_out && x + 1 < x_end) ahead[l] = load_vec<T>(F.prev[l] + row_off + n2);
-    }
-    const PK c = win[(R + u) % NW];
+    for (int l = 0; l < DEPTH; ++l)
+      if (!P.prev_is_src[l]) cur[l] = stage[slot][1 + l][tid];
+    stage_rows(x - x_begin + D);
+    slot = slot + 1 == SLOTS ? 0 : slot + 1;
+    const PK c = win[(R + u) % NP];
     // window along the contiguous axis: HL vectors | the lane's vector | HL vectors
     T zw[(2 * HL + 1) * VN];
 #pragma unroll
@@ -119,7 +147,7 @@ star_row_kernel(const __grid_constant__ StarParams<T> P) {
       dz = row_scale<T, SCALE>(dz, az);
       T dx = (T)0;
 #pragma unroll
-      for (int p = 0; p < NP; ++p) dx = add_rn(dx, mul_rn(ax.w[p], win[(p + u) % NW].v[e]));
+      for (int p = 0; p < NP; ++p) dx = add_rn(dx, mul_rn(ax.w[p], win[(p + u) % NP].v[e]));
       dx = row_scale<T, SCALE>(dx, ax);
       if (is_out) saw_inf |= is_inf(dz) | is_inf(dx);
       rhs.v[e] = mul_rn(add_rn(dx, dz), P.mul);      // canonical order: marched axis, then the contiguous one
@@ -142,11 +170,12 @@ star_row_kernel(const __grid_constant__ StarParams<T> P) {
     }
     row_off += n2;
   };
-  for (int x = x_begin; x < x_end; x += NW) {
+  for (int x = x_begin; x < x_end; x += NP) {
 #pragma unroll
-    for (int u = 0; u < NW; ++u)
+    for (int u = 0; u < NP; ++u)
       if (x + u < x_end) body(u, x + u);
   }
+  cp_async_wait<0>();
   if (saw_inf) raise_flag(F.flags, FD_FLAG_INF);
   warp_add_count(F.nan_count[0], nan_cnt[0]);
   if (DEPTH > 1) warp_add_count(F.nan_count[1], nan_cnt[1]);
