@@ -215,9 +215,11 @@ bool try_star_row(StarParams<T>& P, int axes, cudaStream_t stream) {
     if (F.box_lo[2] % VN != 0 || F.box_hi[2] % VN != 0 || F.n[2] / VN < 32) return false;
     const int segs = (vecs + OUTL - 1) / OUTL;
     const unsigned gx = (segs + 3) / 4;
-    // long marches: the 2R rows around a chunk are read twice (2R/chunk of one level);
-    // shorter ones while the grid would leave SMs without a block
-    int chunk = 64;
+    // the 2R rows around a chunk are read twice (2R/chunk of one level), longer
+    // marches leave fewer blocks for the last wave: 8192^2 radius 4 measured
+    // 0.352 / 0.351 / 0.358 / 0.365 / 0.393 ms with 16 / 32 / 64 / 128 / 256 rows
+    // (profiles/r02_c4_row_chunks.txt); shorter while SMs would be left without a block
+    int chunk = 32;
     while (chunk > 8 && (int64_t)gx * ((nx + chunk - 1) / chunk) < 148 * 4) chunk >>= 1;
     if (const int forced = tuning_chunk()) chunk = forced;
     while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;

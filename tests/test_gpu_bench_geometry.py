@@ -76,7 +76,7 @@ def test_config4_8192_squared_wave_radius4(fd):
     u, _, _ = O.run_wave(shape, 3, 0.01, bench.DT, ic, np.zeros(shape))
     assert np.array_equal(got, u[2], equal_nan=True)
     assert stats["fused"] == 2 and stats["unfused_statements"] == 0
-    assert seen and all(s.startswith("star_row f64 R=4 depth=2") and "chunk=64" in s for s in seen), seen
+    assert seen and all(s.startswith("star_row f64 R=4 depth=2") and "chunk=32" in s for s in seen), seen
 
 
 def test_config5_slab_marching_pair_kernel_default_chunk(fd):
