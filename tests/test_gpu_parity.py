@@ -486,3 +486,33 @@ def test_more_than_three_spatial_axes_fused(fd):
         assert np.array_equal(got, want, equal_nan=True), (shape, periodic)
         if periodic:
             assert stats["fused"] == 3 and stats["unfused_statements"] == 0, (shape, stats)
+
+
+def test_general_power_is_within_the_stated_bound():
+    """`**` with a general exponent is CUDA's pow (not correctly rounded, as is
+    numpy's libm pow): not bit-identical to the reference, but inside the 1e-12
+    relative bound of the north star -- in practice a couple of ulp.  numpy's
+    scalar-exponent fast paths (**2, **0.5, **-1, **1) ARE reproduced exactly."""
+    import torch
+    import finite_difference._native as nat
+    rng = np.random.default_rng(77)
+    n = 1 << 18
+    a = np.abs(rng.standard_normal(n)) * 10.0 ** rng.integers(-3, 4, n) + 1e-6
+    b = rng.uniform(-3.0, 3.0, n)
+    da, db = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    out = torch.empty_like(da)
+    worst = 0.0
+    for s in (1.5, 3.0, -2.5, 0.3333333333333333, 7.0):
+        nat.check(nat.lib.fd_ewise_f64(nat.OP_POW_FS, out.data_ptr(), da.data_ptr(), 0, s, n, 0))
+        got, want = out.cpu().numpy(), a ** s
+        rel = np.max(np.abs(got - want) / np.abs(want))
+        worst = max(worst, rel)
+        assert rel <= 1e-12, (s, rel)
+    nat.check(nat.lib.fd_ewise_f64(nat.OP_POW_FF, out.data_ptr(), da.data_ptr(), db.data_ptr(), 0.0, n, 0))
+    got, want = out.cpu().numpy(), a ** b
+    rel = np.max(np.abs(got - want) / np.abs(want))
+    assert rel <= 1e-12, rel
+    assert max(worst, rel) <= 8 * np.finfo(np.float64).eps          # what it really is: a few ulp
+    for op, ref in ((nat.OP_SQUARE, a * a), (nat.OP_SQRT, np.sqrt(a)), (nat.OP_RECIP, 1.0 / a), (nat.OP_COPY, a)):
+        nat.check(nat.lib.fd_ewise_f64(op, out.data_ptr(), da.data_ptr(), 0, 0.0, n, 0))
+        assert np.array_equal(out.cpu().numpy(), ref)
