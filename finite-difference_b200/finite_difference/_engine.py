@@ -305,6 +305,7 @@ class Engine:
         self.last_poll = model.time_step
         self.pending_copies = []          # [(state, slot, t, host tensor, event)]
         self._ghost_readers = {}          # id(field) -> statements of the current step that read its ghost planes
+        self._stmt_info = {}              # statement key -> (fields read at the new level, ghost reads relative to t)
         self._events, self._event_next = [], 0     # transient events (recorded and waited for within one call)
         self._halo_done = None            # comm stream: the exchange issued last has completed
         self.closed = False
@@ -412,14 +413,24 @@ class Engine:
             self.state(f)
         reads_new = set()
         self._ghost_readers = readers = {}
-        for _, _, node in stmts:
+        keys = [None] * len(stmts)
+        for i, (_, _, node) in enumerate(stmts):
             if node is not None:
-                _collect_new_reads(node, t + 1, reads_new)
+                # what the statement reads depends on its form alone (levels relative to
+                # the time cursor): worked out once per form, looked up by its key
+                keys[i] = key = node.key()
+                info = self._stmt_info.get(key)
+                if info is None:
+                    new_reads, ghosts = set(), set()
+                    _collect_new_reads(node, t + 1, new_reads)
+                    _collect_ghost_reads(node, ghosts)
+                    if len(self._stmt_info) >= 256:
+                        self._stmt_info.clear()
+                    info = self._stmt_info[key] = (frozenset(new_reads), tuple((f, lt - t) for f, lt in ghosts))
+                reads_new |= info[0]
                 if self.H:
-                    seen = set()
-                    _collect_ghost_reads(node, seen)
-                    for key in seen:
-                        readers[key] = readers.get(key, 0) + 1
+                    for f, rel in info[1]:
+                        readers[(f, t + rel)] = readers.get((f, t + rel), 0) + 1
         memo = {}
         consumed = set()
         if self.fuse and self.fuse_pairs and self._try_pair(stmts, t, reads_new):
@@ -432,7 +443,7 @@ class Engine:
                 # (an empty chain: an auxiliary field such as a flux, or a .dot that
                 # is not integrated in this step -- the statement is still one launch)
                 chain = self._find_chain(stmts, i, field)
-                if self.fuse and (chain or self.fuse_aux) and self._try_fused(field, node, chain, t, reads_new):
+                if self.fuse and (chain or self.fuse_aux) and self._try_fused(field, node, chain, t, reads_new, keys[i]):
                     consumed.update(j for j, _ in chain)
                     self.stats["fused"] += 1
                     continue
@@ -626,10 +637,10 @@ class Engine:
         else:
             nat.check(self._fn["fd_fused_expr"](C.byref(top), self.stream))
 
-    def _try_fused(self, dot_field, node, chain, t, reads_new):
+    def _try_fused(self, dot_field, node, chain, t, reads_new, node_key=None):
         # the same statement comes back every step: its launch descriptor is
         # built once per ring parity and only the per-step words are patched
-        key = (id(dot_field), t & 1, tuple(id(p) for _, p in chain), node.key())
+        key = (id(dot_field), t & 1, tuple(id(p) for _, p in chain), node_key if node_key is not None else node.key())
         plan = self._plans.get(key)
         if plan is None:
             plan = self._build_fused_plan(dot_field, node, chain, t)

@@ -89,6 +89,15 @@ class Der(Node):
     def key(self):
         return ("der", self.axis, self.shifts, self.weights, float(self.scale), self.periodic, self.a.key())
 
+    def with_operand(self, a):
+        """The same derivative of another operand of the same shape (Stencil.der memo)."""
+        n = Der.__new__(Der)
+        n.shape, n.dev, n.epoch = self.shape, None, -1
+        n.a, n.axis, n.shifts, n.weights, n.scale = a, self.axis, self.shifts, self.weights, self.scale
+        n.periodic, n.lo, n.hi, n.n_src, n.n_dst = self.periodic, self.lo, self.hi, self.n_src, self.n_dst
+        n.stencil, n.slab = self.stencil, self.slab
+        return n
+
 
 class FieldInstant:
     """Field at one instant of time (FD.py:774-788).  Same attributes as the

@@ -139,8 +139,11 @@ instead first use the assign_update method and then use the new property"
         return self._instant(self.model.time_step)
 
     def _instant(self, t):
-        self._check_index({self.model.time_axis: t})
-        return FieldInstant(self.model, self.edge_axes, self.name, Leaf(self, t))
+        model = self.model
+        # (_check_index for the time axis alone, FD.py:596-604)
+        assert model._lengths[model._t_pos] > t, \
+            f"{model.time_axis} goes out of bounds, it has length {model._lengths[model._t_pos]}"
+        return FieldInstant(model, self.edge_axes, self.name, Leaf(self, t))
 
     def _check_index(self, idxs):
         # FD.py:596-604

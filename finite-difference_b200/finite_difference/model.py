@@ -55,6 +55,8 @@ class Model:
         self._names = list(axes.keys())
         self._lengths = [len(v) for v in axes.values()]
         self._steps = [v[1] - v[0] for v in axes.values()]
+        self._token = object()          # identity of this model in memo keys (ids can be reused, this cannot)
+        self._t_pos = self._names.index(time_axis)
         self.periodic = periodic
         self.time_step = 0
         self.time_axis = time_axis
