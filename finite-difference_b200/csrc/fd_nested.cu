@@ -59,6 +59,43 @@ static int plan_nested(int inner_is_expr, const void* inner, int outer_is_expr, 
 
 }  // namespace fdb
 
+// ---- scratch level inside the library (fd_fused_nested_static_f64) ---------------
+//
+// For hosts that cannot hand over device memory of their own at this point (see
+// fd_b200.h).  The array is part of the loaded module: every GPU that loads the
+// library holds these bytes until the process ends, whether the entry point is
+// ever called or not -- hence the modest size.
+static __device__ __align__(256) unsigned char g_static_scratch[FD_STATIC_SCRATCH_BYTES];
+
+namespace fdb {
+
+// In host code `g_static_scratch` is only a handle for the runtime, not an address
+// a kernel could use: the device address is asked for once per device, with that
+// device current, and kept.
+static int static_scratch_address(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* address[kMaxDevices] = {};
+  static std::atomic<int> ready[kMaxDevices] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices)
+    return fail("fd_fused_nested_static: no current CUDA device (%s)", cudaGetErrorString(e));
+  if (!ready[dev].load(std::memory_order_acquire)) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail("fd_fused_nested_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    }
+    address[dev] = p;          // (two threads racing here store the same value)
+    ready[dev].store(1, std::memory_order_release);
+  }
+  *out = address[dev];
+  return 0;
+}
+
+}  // namespace fdb
+
 using namespace fdb;
 
 #define FD_NESTED(SFX)                                                                                              \
@@ -85,6 +122,24 @@ int fd_fused_nested_f32(int inner_is_expr, const void* inner, int outer_is_expr,
   NestedPlan p;
   if (plan_nested(inner_is_expr, inner, outer_is_expr, outer, scratch, scratch_elems, &p)) return 1;
   return run_nested_f32(p, stream);
+}
+
+int fd_fused_nested_static_f64(int inner_is_expr, const void* inner, int outer_is_expr, const void* outer, void* stream) {
+  // the size test comes first: an expression that does not fit is refused before
+  // anything touches the device
+  if (inner) {
+    const fd_fused_t* in = inner_is_expr ? &((const fd_expr_t*)inner)->base : (const fd_fused_t*)inner;
+    const long long elems = (long long)in->n[0] * in->n[1] * in->n[2];
+    if (elems > (long long)(FD_STATIC_SCRATCH_BYTES / sizeof(double)))
+      return fail("fd_fused_nested_static_f64: the inner expression has %lld values, the built-in scratch level holds %lld "
+                  "(FD_STATIC_SCRATCH_BYTES = %d); use fd_fused_nested_f64 with a scratch level of your own",
+                  elems, (long long)(FD_STATIC_SCRATCH_BYTES / sizeof(double)), (int)FD_STATIC_SCRATCH_BYTES);
+  }
+  void* scratch = nullptr;
+  if (static_scratch_address(&scratch)) return 1;
+  NestedPlan p;
+  if (plan_nested(inner_is_expr, inner, outer_is_expr, outer, scratch, FD_STATIC_SCRATCH_BYTES / sizeof(double), &p)) return 1;
+  return run_nested_f64(p, stream);
 }
 
 }  // extern "C"

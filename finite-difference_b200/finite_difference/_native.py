@@ -116,6 +116,8 @@ SIGNATURES = {
                                C.c_longlong, C.c_void_p]),
     "fd_halo_wait": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p]),
 }
+SIGNATURES["fd_fused_nested_static_f64"] = (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p])
+FD_STATIC_SCRATCH_BYTES = 16 * 1024 * 1024
 for _sfx in ("f64", "f32"):
     SIGNATURES.update({
         f"fd_der_{_sfx}": (_I, [_P, _P, _I64, _I64, _I64, _I64, C.POINTER(Stencil), _I, _I64, _I64, _P, _P]),

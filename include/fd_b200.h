@@ -331,6 +331,31 @@ int fd_fused_nested_f64(int inner_is_expr, const void* inner, int outer_is_expr,
 int fd_fused_nested_f32(int inner_is_expr, const void* inner, int outer_is_expr, const void* outer, void* scratch,
                         long long scratch_elems, void* stream);
 
+/* fd_fused_nested_f64 for callers that have no device memory to give at this
+ * point.  It has no counterpart in the reference (numpy allocates the inner
+ * array afresh on every call) and no counterpart among the other entry points,
+ * which all work on buffers the caller owns.  Meant for hosts that embed the
+ * stepper and may not allocate while they step: an application that handed the
+ * whole GPU to a memory pool of its own when it started, or one whose time
+ * loop must stay free of cudaMalloc because that call synchronises the device
+ * and can still fail late, when memory has become fragmented.  Such a caller
+ * still owns every input and output level; only the scratch level comes from
+ * the library: a fixed array of FD_STATIC_SCRATCH_BYTES that is part of the
+ * loaded module (each GPU that loads the library carries it until the process
+ * ends).  The function allocates nothing, on the host or on the device.
+ *   - The inner expression may have at most FD_STATIC_SCRATCH_BYTES / 8 values
+ *     (2 Mi doubles, e.g. a 1448 x 1448 or a 128^3 level); anything larger is
+ *     refused with an error before any launch.
+ *   - The first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current) and keeps it; make that
+ *     first call outside any stream capture.
+ *   - All calls on a device share the one array.  Nothing in it has to be
+ *     cleared between calls -- the inner launch writes every value the outer
+ *     launch reads -- but two calls whose launches can overlap on the GPU
+ *     (different streams, no ordering between them) race on it: order them. */
+#define FD_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
+int fd_fused_nested_static_f64(int inner_is_expr, const void* inner, int outer_is_expr, const void* outer, void* stream);
+
 /* ---- halo exchange over peer memory (multi-GPU slabs) --------------------
  *
  * No reference counterpart: the reference is a single-process numpy program.
