@@ -245,6 +245,16 @@ class PeerLinks:
         self.nat.check(self.nat.lib.fd_halo_wait(self.my_lo[k], self.my_hi[k], self.base + value, self.TIMEOUT_NS,
                                                  err_flags, stream))
 
+    def fill(self, link, k, value):
+        """Describe the exchange of ring slot ``k`` at level number ``value`` in a
+        ``fd_halo_link_t`` (fd_halo_exchange / fd_slab_step)."""
+        link.src_lo, link.peer_dst_lo = self.src_lo[k], self.dst_lo[k]
+        link.src_hi, link.peer_dst_hi = self.src_hi[k], self.dst_hi[k]
+        link.nbytes = self.nbytes
+        link.peer_flag_lo, link.peer_flag_hi = self.flag_lo[k], self.flag_hi[k]
+        link.my_flag_lo, link.my_flag_hi = self.my_lo[k], self.my_hi[k]
+        link.value = self.base + value
+
     @classmethod
     def close_all(cls, nat):
         """Unmap every neighbour buffer this process opened (process exit)."""

@@ -177,7 +177,10 @@ class FieldState:
             self.engine.stats["halo_exchanges"] = self.engine.stats.get("halo_exchanges", 0) + 1
         elif self.halo_event[k] is not None:
             # exchanged ahead of time on the comm stream: order the consumer after it
-            self.engine.dev.stream.wait_event(self.halo_event[k])
+            if self.halo_event[k] == "seq":        # issued natively (fd_slab_step): its event lives in the library
+                nat.check(nat.lib.fd_seq_wait_halo(self.engine.seq, self.engine.stream))
+            else:
+                self.engine.dev.stream.wait_event(self.halo_event[k])
             self.halo_event[k] = None
 
     # -- boundary faces ------------------------------------------------------
@@ -308,6 +311,10 @@ class Engine:
         self._stmt_info = {}              # statement key -> (fields read at the new level, ghost reads relative to t)
         self._events, self._event_next = [], 0     # transient events (recorded and waited for within one call)
         self._halo_done = None            # comm stream: the exchange issued last has completed
+        self.seq = None                   # native sequencer of slab steps (fd_seq_create), made on first use
+        self.native_seq = os.environ.get("FD_B200_NO_SEQ", "0") != "1"
+        self._seq_steps = {}              # id(descriptor) -> (fd_slab_step_t, states in link order) or None
+        self._ticket = None               # device word of fd_halo_exchange
         self.closed = False
         self._box_cache = {}
         self._plans = {}                  # statement key -> launch descriptor (see _try_fused)
@@ -374,6 +381,10 @@ class Engine:
         except Exception:
             return
         from ._dist import RingPool
+        if self.seq is not None:
+            nat.lib.fd_seq_destroy(self.seq)
+            self.seq = None
+        self._seq_steps = {}
         for st in self.states.values():
             if st.peer:
                 st.peer.retire(self.n_t)
@@ -649,6 +660,7 @@ class Engine:
             if len(self._plans) >= 64:      # e.g. a coefficient that changes every step
                 self._plans.clear()
                 self._box_cache.clear()
+                self._seq_steps.clear()
             self._plans[key] = plan
         d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux, inner_plans, nested = plan
         for src_state, offset, slab in sources:
@@ -657,6 +669,7 @@ class Engine:
             except RuntimeError:
                 del self._plans[key]
                 self._box_cache.clear()
+                self._seq_steps.clear()
                 return False
             if slab:
                 src_state.refresh_ghosts(t + offset)
@@ -730,12 +743,65 @@ class Engine:
             # of the field it advances (see _exchange_ahead)
             own = {id(st) for st, offset, slab in sources if slab and offset == 0}
             self._run_overlapped(run, region, pad, eager, t,
-                                 {id(ls) for ls in eager if id(ls) in own and not aux and self._sole_ghost_reader(ls, t)})
+                                 {id(ls) for ls in eager if id(ls) in own and not aux and self._sole_ghost_reader(ls, t)},
+                                 seq_desc=(0, d, d, key) if top is None else (2, top, d, key))
         else:
             run(region)
         return True
 
-    def _run_overlapped(self, run, region, pad, eager, t, direct_ok=()):
+    def _native_slab_step(self, seq_desc, region, pad, eager, t, direct_ok):
+        """The whole of _run_overlapped in one native call (fd_slab_step) when every
+        exchanged field travels through peer memory and no piece needs an
+        interior/rim split; False if the statement has to take the Python path."""
+        kind, d, base_desc, cache_key = seq_desc
+        dev = self.dev
+        if not (self.native_seq and self.peer_halo and self.rims_beside and dev.comm_stream is not None):
+            return False
+        for st in eager:                    # collective set-up, first use only
+            if st.peer is None and id(st) in direct_ok and len(st.ring) > 1:
+                st.peer = self._peer_links(st)
+        if not all(st.peer and id(st) in direct_ok for st in eager) or len(eager) > nat.FD_MAX_LINKS:
+            return False
+        cached = self._seq_steps.get(cache_key, 0)
+        if cached == 0:
+            cached = None
+            lo, hi = region[pad]
+            pieces = [[lo, lo + self.H], [hi - self.H, hi], [lo + self.H, hi - self.H]]
+            whole = lambda cut: [list(r) if a != pad else cut for a, r in enumerate(region)]
+            single = kind != 0 or all(len(self._split_boxes(base_desc, whole(c))) == 1 for c in pieces)
+            if single:
+                step = nat.SlabStep()
+                step.kind, step.dim, step.lo, step.hi, step.depth = kind, pad, lo, hi, self.H
+                step.nlinks = len(eager)
+                step.timeout_ns = 20_000_000_000
+                step.flags = self.flags.data_ptr()
+                cached = (step, list(eager))
+            self._seq_steps[cache_key] = cached
+        if cached is None:
+            return False
+        step, states = cached
+        if [id(s) for s in states] != [id(s) for s in eager]:
+            return False
+        if self.seq is None:
+            handle = C.c_void_p()
+            nat.check(nat.lib.fd_seq_create(C.byref(handle)))
+            self.seq = handle
+        for a in range(3):
+            base_desc.box_lo[a], base_desc.box_hi[a] = region[a]
+        for j, st in enumerate(eager):
+            st.peer.fill(step.link[j], st.slot_index(t + 1), t + 2)
+        step.desc = C.addressof(d)
+        step.compute_stream, step.comm_stream = self.stream, dev.comm_stream.cuda_stream
+        nat.check(nat.fn("fd_slab_step", self.dtype)(self.seq, C.byref(step)))
+        for st in eager:
+            k = st.slot_index(t + 1)
+            st.halo_ok[k], st.halo_event[k] = True, "seq"
+        self.stats["halo_exchanges"] = self.stats.get("halo_exchanges", 0) + len(eager)
+        self.stats["peer_halo_exchanges"] = self.stats.get("peer_halo_exchanges", 0) + len(eager)
+        self.stats["native_slab_steps"] = self.stats.get("native_slab_steps", 0) + 1
+        return True
+
+    def _run_overlapped(self, run, region, pad, eager, t, direct_ok=(), seq_desc=None):
         """One statement (group) of a slab: the boundary planes and their exchange
         on the high-priority comm stream, the interior beside them on the compute
         stream, so that neither the thin boundary launches nor the trip over
@@ -745,6 +811,8 @@ class Engine:
         cuts = ([lo, lo + self.H], [hi - self.H, hi])
         inner = [lo + self.H, hi - self.H]
         dev = self.dev
+        if seq_desc is not None and self._native_slab_step(seq_desc, region, pad, eager, t, direct_ok):
+            return
         if dev.comm_stream is None or not self.rims_beside:
             # (CPU stand-in, or FD_B200_NO_SIDE_RIMS=1) boundary planes first, their
             # exchange on the comm stream, then the interior while the planes travel
@@ -802,16 +870,20 @@ class Engine:
             if not on_comm:
                 dev.comm_stream.wait_event(ready)
             cs = dev.comm_stream.cuda_stream
-            direct = [st for st in states if st.peer and id(st) in direct_ok]
-            # peer memory: every push first, then the waits (a wait holds the stream)
-            for st in direct:
-                st.peer.push(st.slot_index(t), t + 1, cs)
+            direct = [st for st in states if st.peer and id(st) in direct_ok][:nat.FD_MAX_LINKS]
+            # peer memory: copy, publication and wait of all fields in one launch
+            if direct:
+                if self._ticket is None:
+                    self._ticket = dev.zeros_i64(1)
+                links = (nat.HaloLink * len(direct))()
+                for j, st in enumerate(direct):
+                    st.peer.fill(links[j], st.slot_index(t), t + 1)
+                nat.check(nat.lib.fd_halo_exchange(links, len(direct), self._ticket.data_ptr(), 20_000_000_000,
+                                                   self.flags.data_ptr(), cs))
             for st in states:
                 if st not in direct:
                     k = st.slot_index(t)
                     self.slab.exchange(st.ring[k], st.plane, st.owned0, st.H)
-            for st in direct:
-                st.peer.wait(st.slot_index(t), t + 1, self.flags.data_ptr(), cs)
             if direct:
                 self.stats["peer_halo_exchanges"] = self.stats.get("peer_halo_exchanges", 0) + len(direct)
             # one event, always recorded on the comm stream: a consumer that waits
@@ -1026,7 +1098,7 @@ class Engine:
         if eager and self.overlap:
             # (the pair kernel reads the level-t ghosts of p and of the slab-axis velocity,
             # and the statements it replaces are the only ones of the step)
-            self._run_overlapped(run, region, pad, eager, t, {id(st) for st in eager})
+            self._run_overlapped(run, region, pad, eager, t, {id(st) for st in eager}, seq_desc=(1, d, d, ("pair", t & 1, len(terms))))
         else:
             run(region)
         return True
@@ -1221,6 +1293,7 @@ class Engine:
     def host_changed(self, field):
         self._plans.clear()
         self._box_cache.clear()
+        self._seq_steps.clear()
         st = self.states.get(id(field))
         if st is not None:
             st.faces = None

@@ -101,6 +101,22 @@ class Expr(C.Structure):
                 ("imm", C.c_double * FD_EXPR_MAX_CODE)]
 
 
+FD_MAX_LINKS = 4
+
+
+class HaloLink(C.Structure):
+    _fields_ = [("src_lo", C.c_void_p), ("peer_dst_lo", C.c_void_p), ("src_hi", C.c_void_p), ("peer_dst_hi", C.c_void_p),
+                ("nbytes", C.c_longlong), ("peer_flag_lo", C.c_void_p), ("peer_flag_hi", C.c_void_p),
+                ("my_flag_lo", C.c_void_p), ("my_flag_hi", C.c_void_p), ("value", C.c_longlong)]
+
+
+class SlabStep(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("dim", C.c_int32), ("lo", C.c_int32), ("hi", C.c_int32),
+                ("depth", C.c_int32), ("nlinks", C.c_int32), ("desc", C.c_void_p),
+                ("link", HaloLink * FD_MAX_LINKS), ("timeout_ns", C.c_longlong), ("flags", C.c_void_p),
+                ("compute_stream", C.c_void_p), ("comm_stream", C.c_void_p)]
+
+
 _I64, _P, _D, _I = C.c_int64, C.c_void_p, C.c_double, C.c_int
 
 # name -> (restype, argtypes); every symbol include/fd_b200.h declares
@@ -115,6 +131,12 @@ SIGNATURES = {
     "fd_halo_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p,
                                C.c_longlong, C.c_void_p]),
     "fd_halo_wait": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_longlong, C.c_void_p, C.c_void_p]),
+    "fd_halo_exchange": (C.c_int, [C.POINTER(HaloLink), C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p]),
+    "fd_seq_create": (C.c_int, [C.POINTER(C.c_void_p)]),
+    "fd_seq_destroy": (C.c_int, [C.c_void_p]),
+    "fd_seq_wait_halo": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "fd_slab_step_f64": (C.c_int, [C.c_void_p, C.POINTER(SlabStep)]),
+    "fd_slab_step_f32": (C.c_int, [C.c_void_p, C.POINTER(SlabStep)]),
 }
 SIGNATURES["fd_fused_nested_static_f64"] = (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p])
 FD_STATIC_SCRATCH_BYTES = 16 * 1024 * 1024

@@ -383,6 +383,54 @@ int fd_halo_push(const void* src_lo, void* peer_dst_lo, const void* src_hi, void
                  void* peer_flag_lo, void* peer_flag_hi, long long value, void* stream);
 int fd_halo_wait(const void* flag_a, const void* flag_b, long long value, long long timeout_ns, void* flags, void* stream);
 
+/* fd_halo_exchange: push + publish + wait of up to FD_MAX_LINKS fields in ONE
+ *   launch.  Every block copies its share, the block that finishes last publishes
+ *   `value` in the neighbours' flag words and then waits for this rank's own
+ *   words (same time-out behaviour as fd_halo_wait).  `counter` is a device
+ *   uint32 the caller zeroes once; the kernel leaves it zero.  Launches that
+ *   share a counter must be ordered (same stream). */
+#define FD_MAX_LINKS 4
+typedef struct fd_halo_link {
+  const void* src_lo;      /* this rank's lowest owned planes  -> peer_dst_lo (previous rank's high ghosts) */
+  void* peer_dst_lo;
+  const void* src_hi;      /* this rank's highest owned planes -> peer_dst_hi (next rank's low ghosts)      */
+  void* peer_dst_hi;
+  long long nbytes;        /* per side, a multiple of 16 */
+  void* peer_flag_lo;      /* the neighbours' flag words that receive `value` */
+  void* peer_flag_hi;
+  const void* my_flag_lo;  /* this rank's flag words to wait on (>= value)    */
+  const void* my_flag_hi;
+  long long value;
+} fd_halo_link_t;
+int fd_halo_exchange(const fd_halo_link_t* links, int nlinks, void* counter, long long timeout_ns, void* flags, void* stream);
+
+/* One statement of a slab step, issued natively (the reference has neither
+ * slabs nor streams): the interior box [lo+depth, hi-depth) of `desc` along the
+ * decomposed dimension on the compute stream; the two boundary boxes of `depth`
+ * planes and then fd_halo_exchange of `link[]` on the communication stream;
+ * the events that order the two streams.  Afterwards the compute stream has
+ * waited for the boundary boxes but not for the exchange: fd_seq_wait_halo
+ * makes a stream wait for the exchange issued last.  `seq` (fd_seq_create)
+ * holds the events and the ticket counter; one per process and device. */
+typedef struct fd_slab_step {
+  int32_t kind;            /* descriptor type: 0 fd_fused_t, 1 fd_pair_t, 2 fd_expr_t */
+  int32_t dim;             /* decomposed dimension of the collapsed view */
+  int32_t lo, hi;          /* owned planes along it: [lo, hi), hi - lo >= 3 * depth */
+  int32_t depth;           /* ghost planes on either side */
+  int32_t nlinks;          /* fields whose new boundary planes travel (0: none) */
+  const void* desc;        /* box_lo/box_hi of the other dimensions are taken from it */
+  fd_halo_link_t link[FD_MAX_LINKS];
+  long long timeout_ns;
+  void* flags;
+  void* compute_stream;
+  void* comm_stream;
+} fd_slab_step_t;
+int fd_seq_create(void** seq_out);
+int fd_seq_destroy(void* seq);
+int fd_seq_wait_halo(void* seq, void* stream);
+int fd_slab_step_f64(void* seq, const fd_slab_step_t* step);
+int fd_slab_step_f32(void* seq, const fd_slab_step_t* step);
+
 #ifdef __cplusplus
 }
 #endif

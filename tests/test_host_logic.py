@@ -229,6 +229,16 @@ def test_peer_links_address_arithmetic():
                 assert push[1:] == want_push
                 assert wait[1:] == (flag_addr(r) + 2 * k * 8 if prev is not None else None,
                                     flag_addr(r) + (2 * k + 1) * 8 if nxt is not None else None, 11, links.TIMEOUT_NS, 123, 0)
+                # the same exchange as one fd_halo_link_t (fd_halo_exchange / fd_slab_step), after a
+                # retired model: level numbers continue above everything the old model published
+                import finite_difference._native as real_nat
+                link = real_nat.HaloLink()
+                links.retire(40)
+                links.fill(link, k, 11)
+                assert (link.src_lo, link.peer_dst_lo, link.src_hi, link.peer_dst_hi, link.nbytes, link.peer_flag_lo,
+                        link.peer_flag_hi) == want_push[:7]
+                assert (link.my_flag_lo, link.my_flag_hi) == wait[1:3] and link.value == 11 + links.base
+                assert links.base == 42 * (k + 1)
     # planes that are not multiples of 16 bytes: the field keeps isend/irecv, on every rank
     slab = Slab()
     slab.world, slab.rank, slab.prev_rank, slab.next_rank = 2, 0, 1, 1
