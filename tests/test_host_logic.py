@@ -212,6 +212,7 @@ def test_peer_links_address_arithmetic():
             assert links.ok and links.nbytes == H * plane_bytes
             mapped = lambda q, addr: addr + 0x7000_0000_0000
             for k in range(2):
+                level = 11 + links.base             # (the second round comes after a retired model)
                 links.push(k, 11, 0)
                 links.wait(k, 11, 123, 0)
                 push, wait = calls[-2], calls[-1]
@@ -225,10 +226,10 @@ def test_peer_links_address_arithmetic():
                     H * plane_bytes,
                     mapped(prev, flag_addr(prev)) + (2 * k + 1) * 8 if prev is not None else None,        # "your high ghost is fresh"
                     mapped(nxt, flag_addr(nxt)) + (2 * k) * 8 if nxt is not None else None,               # "your low ghost is fresh"
-                    11, 0)
+                    level, 0)
                 assert push[1:] == want_push
                 assert wait[1:] == (flag_addr(r) + 2 * k * 8 if prev is not None else None,
-                                    flag_addr(r) + (2 * k + 1) * 8 if nxt is not None else None, 11, links.TIMEOUT_NS, 123, 0)
+                                    flag_addr(r) + (2 * k + 1) * 8 if nxt is not None else None, level, links.TIMEOUT_NS, 123, 0)
                 # the same exchange as one fd_halo_link_t (fd_halo_exchange / fd_slab_step), after a
                 # retired model: level numbers continue above everything the old model published
                 import finite_difference._native as real_nat
