@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
+# (FD_B200_LIB: another build of the same library, for A/B runs of kernel variants)
+LIB_PATH = os.environ.get("FD_B200_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libfd_b200.so")
 
 ABI_VERSION = 6
 FD_MAX_POINTS = 16
