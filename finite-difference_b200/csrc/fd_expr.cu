@@ -15,7 +15,7 @@
 
 namespace fdb {
 
-constexpr int kExprThreads = 256;
+constexpr int kExprThreads = 128;
 
 template <typename T>
 struct DevExpr {
@@ -61,46 +61,96 @@ __device__ __forceinline__ T der_at(const DevTerm<T>& tm, int i0, int i1, int i2
   return d;
 }
 
-template <typename T>
+// PT points per thread along the contiguous axis (consecutive points of a thread
+// lie blockDim.x apart, so every access of a warp stays one contiguous run): the
+// program is decoded once per PT points instead of once per point, and the top of
+// the stack lives in registers, so a binary operation reads one operand from
+// shared memory instead of reading two and writing one.  (One point per thread
+// and everything on the shared-memory stack: Burgers 2-D at 8192^2 took 2.55 ms,
+// ~1000 instructions per point, issue-bound; profiles/r02_expr_burgers_before_*.)
+template <typename T, int PT>
 __global__ void __launch_bounds__(kExprThreads)
 expr_kernel(const __grid_constant__ DevExpr<T> P) {
-  __shared__ T stack[FD_EXPR_MAX_STACK][kExprThreads];
+  __shared__ T stack[FD_EXPR_MAX_STACK - 1][PT][kExprThreads];
   const DevFused<T>& F = P.F;
   const int n1 = F.n[1], n2 = F.n[2];
   const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-  const int i2 = blockIdx.x * blockDim.x + threadIdx.x;
-  const int i1 = blockIdx.y * blockDim.y + threadIdx.y;
-  const bool active = i2 >= F.box_lo[2] && i2 < F.box_hi[2] && i1 >= F.box_lo[1] && i1 < F.box_hi[1];
+  const int i2_0 = F.box_lo[2] + blockIdx.x * (blockDim.x * PT) + threadIdx.x;
+  const int i1 = F.box_lo[1] + blockIdx.y * blockDim.y + threadIdx.y;
+  const bool row_active = i1 < F.box_hi[1];
+  bool active[PT];
+#pragma unroll
+  for (int p = 0; p < PT; ++p) active[p] = row_active && i2_0 + p * (int)blockDim.x < F.box_hi[2];
   unsigned nan_cnt[2] = {0u, 0u};
   bool saw_inf = false, clash = false;
 
   for (int i0 = F.box_lo[0] + blockIdx.z * F.x_chunk, i0_end = min(i0 + F.x_chunk, F.box_hi[0]); i0 < i0_end; ++i0) {
-    if (!active) continue;
-    const int64_t idx = ((int64_t)i0 * n1 + i1) * n2 + i2;
+    if (!active[0]) continue;
+    const int64_t idx0 = ((int64_t)i0 * n1 + i1) * n2 + i2_0;
+    T top[PT];
+#pragma unroll
+    for (int p = 0; p < PT; ++p) top[p] = (T)0;
     int sp = 0;   // warp-uniform: every thread runs the same program
+    // spill the register top before something new is pushed
+#define FD_X_SPILL()                                        \
+    if (sp > 0) {                                           \
+      _Pragma("unroll") for (int p = 0; p < PT; ++p) stack[sp - 1][p][tid] = top[p]; \
+    }
     for (int pc = 0; pc < P.ncode; ++pc) {
       const int op = P.op[pc];
-      switch (op) {
-        case FD_X_PUSH_DER: stack[sp++][tid] = der_at<T>(F.term[P.arg[pc]], i0, i1, i2, saw_inf); break;
-        case FD_X_PUSH_FIELD: stack[sp++][tid] = __ldg(P.field[P.arg[pc]] + idx); break;
-        case FD_X_PUSH_IMM: stack[sp++][tid] = P.imm[pc]; break;
-        case FD_X_NEG: stack[sp - 1][tid] = -stack[sp - 1][tid]; break;
-        case FD_X_ADD: --sp; stack[sp - 1][tid] = add_rn(stack[sp - 1][tid], stack[sp][tid]); break;
-        case FD_X_SUB: --sp; stack[sp - 1][tid] = sub_rn(stack[sp - 1][tid], stack[sp][tid]); break;
-        case FD_X_MUL: --sp; stack[sp - 1][tid] = mul_rn(stack[sp - 1][tid], stack[sp][tid]); break;
-        case FD_X_DIV: --sp; stack[sp - 1][tid] = div_rn(stack[sp - 1][tid], stack[sp][tid]); break;
-        case FD_X_POW: --sp; stack[sp - 1][tid] = pow_dev<T>(stack[sp - 1][tid], stack[sp][tid]); break;
-        case FD_X_ADD_IMM: stack[sp - 1][tid] = add_rn(stack[sp - 1][tid], P.imm[pc]); break;
-        case FD_X_SUB_IMM: stack[sp - 1][tid] = sub_rn(stack[sp - 1][tid], P.imm[pc]); break;
-        case FD_X_MUL_IMM: stack[sp - 1][tid] = mul_rn(stack[sp - 1][tid], P.imm[pc]); break;
-        case FD_X_DIV_IMM: stack[sp - 1][tid] = div_rn(stack[sp - 1][tid], P.imm[pc]); break;
-        case FD_X_POW_IMM: stack[sp - 1][tid] = pow_dev<T>(stack[sp - 1][tid], P.imm[pc]); break;
-        case FD_X_SQUARE: stack[sp - 1][tid] = mul_rn(stack[sp - 1][tid], stack[sp - 1][tid]); break;
-        case FD_X_RECIP: stack[sp - 1][tid] = div_rn((T)1, stack[sp - 1][tid]); break;
-        case FD_X_SQRT: stack[sp - 1][tid] = sqrt_dev<T>(stack[sp - 1][tid]); break;
+      if (op <= FD_X_PUSH_IMM) {
+        FD_X_SPILL()
+        ++sp;
+        if (op == FD_X_PUSH_DER) {
+          const DevTerm<T>& tm = F.term[P.arg[pc]];
+#pragma unroll
+          for (int p = 0; p < PT; ++p)
+            if (active[p]) top[p] = der_at<T>(tm, i0, i1, i2_0 + p * (int)blockDim.x, saw_inf);
+        } else if (op == FD_X_PUSH_FIELD) {
+          const T* f = P.field[P.arg[pc]] + idx0;
+#pragma unroll
+          for (int p = 0; p < PT; ++p)
+            if (active[p]) top[p] = __ldg(f + p * (int)blockDim.x);
+        } else {
+#pragma unroll
+          for (int p = 0; p < PT; ++p) top[p] = P.imm[pc];
+        }
+      } else if (op >= FD_X_ADD && op <= FD_X_POW) {
+        --sp;                          // b = top (registers), a = the slot below
+#pragma unroll
+        for (int p = 0; p < PT; ++p) {
+          const T a = stack[sp - 1][p][tid], b = top[p];
+          top[p] = op == FD_X_ADD ? add_rn(a, b)
+                   : op == FD_X_SUB ? sub_rn(a, b)
+                   : op == FD_X_MUL ? mul_rn(a, b)
+                   : op == FD_X_DIV ? div_rn(a, b) : pow_dev<T>(a, b);
+        }
+      } else {
+        const T imm = P.imm[pc];
+#pragma unroll
+        for (int p = 0; p < PT; ++p) {
+          const T a = top[p];
+          T r;
+          switch (op) {
+            case FD_X_NEG: r = -a; break;
+            case FD_X_ADD_IMM: r = add_rn(a, imm); break;
+            case FD_X_SUB_IMM: r = sub_rn(a, imm); break;
+            case FD_X_MUL_IMM: r = mul_rn(a, imm); break;
+            case FD_X_DIV_IMM: r = div_rn(a, imm); break;
+            case FD_X_POW_IMM: r = pow_dev<T>(a, imm); break;
+            case FD_X_SQUARE: r = mul_rn(a, a); break;
+            case FD_X_RECIP: r = div_rn((T)1, a); break;
+            default: r = sqrt_dev<T>(a); break;
+          }
+          top[p] = r;
+        }
       }
     }
-    fused_epilogue(F, stack[0][tid], idx, i0, i1, i2, nan_cnt, clash);
+#undef FD_X_SPILL
+#pragma unroll
+    for (int p = 0; p < PT; ++p)
+      if (active[p])
+        fused_epilogue(F, top[p], idx0 + p * (int)blockDim.x, i0, i1, i2_0 + p * (int)blockDim.x, nan_cnt, clash);
   }
   if (saw_inf) raise_flag(F.flags, FD_FLAG_INF);
   if (clash) raise_flag(F.flags, FD_FLAG_OVERRIDE);
@@ -150,22 +200,31 @@ static int expr_impl(const fd_expr_t* d, void* stream) {
   }
   if (sp != 1) return fail("fd_fused_expr: the program leaves %d values on the stack", sp);
 
-  const int n1 = P.F.box_hi[1] - P.F.box_lo[1], n2 = P.F.n[2], nx = P.F.box_hi[0] - P.F.box_lo[0];
-  if (nx <= 0 || n1 <= 0 || P.F.box_hi[2] <= P.F.box_lo[2]) return 0;
+  const int n1 = P.F.box_hi[1] - P.F.box_lo[1], n2 = P.F.box_hi[2] - P.F.box_lo[2], nx = P.F.box_hi[0] - P.F.box_lo[0];
+  if (nx <= 0 || n1 <= 0 || n2 <= 0) return 0;
   int bx = 32;
   while (bx < 128 && bx < n2) bx <<= 1;
   int by = kExprThreads / bx;
-  while (by > 1 && by / 2 >= P.F.n[1]) by >>= 1;
-  const int64_t gy = (P.F.n[1] + by - 1) / by;
-  if (gy > 65535) return fail("fd_fused_expr: middle dimension %d too large", P.F.n[1]);
+  while (by > 1 && by / 2 >= n1) by >>= 1;
+  // points per thread along the row: 4 on long rows, fewer while blocks would idle
+  int pt = 4;
+  while (pt > 1 && bx * pt > n2) pt >>= 1;
+  const int64_t gy = (n1 + by - 1) / by;
+  if (gy > 65535) return fail("fd_fused_expr: middle dimension %d too large", n1);
+  const int gx = (n2 + bx * pt - 1) / (bx * pt);
   int chunk = 8;
-  while (chunk > 1 && (int64_t)((n2 + bx - 1) / bx) * gy * ((nx + chunk - 1) / chunk) < 148 * 8) chunk >>= 1;
+  while (chunk > 1 && (int64_t)gx * gy * ((nx + chunk - 1) / chunk) < 148 * 8) chunk >>= 1;
   while ((nx + chunk - 1) / chunk > 65535) chunk <<= 1;
   P.F.x_chunk = chunk;
-  dim3 grid((n2 + bx - 1) / bx, (unsigned)gy, (nx + chunk - 1) / chunk), block(bx, by, 1);
-  note_kernel("expr f%d code=%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, P.ncode, chunk, grid.x, grid.y, grid.z,
-              bx, by);
-  expr_kernel<T><<<grid, block, 0, (cudaStream_t)stream>>>(P);
+  dim3 grid(gx, (unsigned)gy, (nx + chunk - 1) / chunk), block(bx, by, 1);
+  note_kernel("expr f%d code=%d pt=%d chunk=%d grid=%ux%ux%u block=%dx%d", (int)sizeof(T) * 8, P.ncode, pt, chunk, grid.x, grid.y,
+              grid.z, bx, by);
+  if (pt == 4)
+    expr_kernel<T, 4><<<grid, block, 0, (cudaStream_t)stream>>>(P);
+  else if (pt == 2)
+    expr_kernel<T, 2><<<grid, block, 0, (cudaStream_t)stream>>>(P);
+  else
+    expr_kernel<T, 1><<<grid, block, 0, (cudaStream_t)stream>>>(P);
   return check_launch("fd_fused_expr");
 }
 
