@@ -61,6 +61,68 @@ __device__ __forceinline__ T der_at(const DevTerm<T>& tm, int i0, int i1, int i2
   return d;
 }
 
+// One der term at the PT points of a thread (i2_0 + p*step): the stencil point is
+// the outer loop, so its shift and weight are fetched once for all PT points.
+template <typename T, int PT>
+__device__ __forceinline__ void ders_at(const DevTerm<T>& tm, int i0, int i1, int i2_0, int step, const bool (&active)[PT],
+                                        T (&out)[PT], bool& saw_inf) {
+  T acc[PT];
+  bool bad[PT];
+#pragma unroll
+  for (int p = 0; p < PT; ++p) {
+    acc[p] = (T)0;
+    bad[p] = false;
+  }
+  if (tm.axis != 2) {          // (warp-uniform) the same index along the axis for all PT points
+    const int j = term_index(tm, i0, i1, i2_0);
+    const bool outside = !tm.periodic && (j < tm.lo || j >= tm.hi);
+    if (!outside) {
+      const int64_t sa = tm.sa;
+      const T* base = tm.src + (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1] + i2_0 - (int64_t)j * sa;
+      for (int q = 0; q < tm.st.npts; ++q) {
+        int jj = j + tm.st.shifts[q];
+        if (tm.periodic) {
+          jj += (jj < 0) ? tm.n_src : 0;
+          jj -= (jj >= tm.n_src) ? tm.n_src : 0;
+        }
+        const T w = tm.st.weights[q];
+        const T* row = base + (int64_t)jj * sa;
+#pragma unroll
+        for (int p = 0; p < PT; ++p)
+          if (active[p]) acc[p] = add_rn(acc[p], mul_rn(w, __ldg(row + p * step)));
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < PT; ++p) bad[p] = outside;
+  } else {
+    const T* row = tm.src + (int64_t)i0 * tm.stride[0] + (int64_t)i1 * tm.stride[1];
+#pragma unroll
+    for (int p = 0; p < PT; ++p) {
+      const int j = i2_0 + p * step;
+      bad[p] = !tm.periodic && (j < tm.lo || j >= tm.hi);
+    }
+    for (int q = 0; q < tm.st.npts; ++q) {
+      const int sh = tm.st.shifts[q];
+      const T w = tm.st.weights[q];
+#pragma unroll
+      for (int p = 0; p < PT; ++p) {
+        int jj = i2_0 + p * step + sh;
+        if (tm.periodic) {
+          jj += (jj < 0) ? tm.n_src : 0;
+          jj -= (jj >= tm.n_src) ? tm.n_src : 0;
+        }
+        if (active[p] && !bad[p]) acc[p] = add_rn(acc[p], mul_rn(w, __ldg(row + jj)));
+      }
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < PT; ++p) {
+    const T d = apply_scale(acc[p], tm.st.div_mode, tm.st.scale, tm.st.inv);
+    saw_inf |= active[p] && !bad[p] && is_inf(d);
+    out[p] = bad[p] ? quiet_nan<T>() : d;
+  }
+}
+
 // PT points per thread along the contiguous axis (consecutive points of a thread
 // lie blockDim.x apart, so every access of a warp stays one contiguous run): the
 // program is decoded once per PT points instead of once per point, and the top of
@@ -87,6 +149,15 @@ expr_kernel(const __grid_constant__ DevExpr<T> P) {
   for (int i0 = F.box_lo[0] + blockIdx.z * F.x_chunk, i0_end = min(i0 + F.x_chunk, F.box_hi[0]); i0 < i0_end; ++i0) {
     if (!active[0]) continue;
     const int64_t idx0 = ((int64_t)i0 * n1 + i1) * n2 + i2_0;
+    // every der term of the statement, once per point (the program may push a term
+    // several times; terms are few, so they wait in registers)
+    T dval[FD_MAX_TERMS][PT];
+#pragma unroll
+    for (int k = 0; k < FD_MAX_TERMS; ++k) {
+#pragma unroll
+      for (int p = 0; p < PT; ++p) dval[k][p] = (T)0;
+      if (k < F.nterms) ders_at<T, PT>(F.term[k], i0, i1, i2_0, (int)blockDim.x, active, dval[k], saw_inf);
+    }
     T top[PT];
 #pragma unroll
     for (int p = 0; p < PT; ++p) top[p] = (T)0;
@@ -96,56 +167,63 @@ expr_kernel(const __grid_constant__ DevExpr<T> P) {
     if (sp > 0) {                                           \
       _Pragma("unroll") for (int p = 0; p < PT; ++p) stack[sp - 1][p][tid] = top[p]; \
     }
+#define FD_X_EACH(EXPR)                                     \
+    _Pragma("unroll") for (int p = 0; p < PT; ++p) {        \
+      const T a = top[p];                                   \
+      top[p] = (EXPR);                                      \
+    }
+#define FD_X_PAIR(EXPR)                                     \
+    --sp;                                                   \
+    _Pragma("unroll") for (int p = 0; p < PT; ++p) {        \
+      const T a = stack[sp - 1][p][tid], b = top[p];        \
+      top[p] = (EXPR);                                      \
+    }
     for (int pc = 0; pc < P.ncode; ++pc) {
       const int op = P.op[pc];
-      if (op <= FD_X_PUSH_IMM) {
-        FD_X_SPILL()
-        ++sp;
-        if (op == FD_X_PUSH_DER) {
-          const DevTerm<T>& tm = F.term[P.arg[pc]];
+      const T imm = P.imm[pc];
+      switch (op) {                 // decoded once for the PT points of the thread
+        case FD_X_PUSH_DER: {
+          FD_X_SPILL()
+          ++sp;
+          const int k = P.arg[pc];
 #pragma unroll
-          for (int p = 0; p < PT; ++p)
-            if (active[p]) top[p] = der_at<T>(tm, i0, i1, i2_0 + p * (int)blockDim.x, saw_inf);
-        } else if (op == FD_X_PUSH_FIELD) {
+          for (int p = 0; p < PT; ++p) top[p] = k == 0 ? dval[0][p] : (k == 1 ? dval[1][p] : (k == 2 ? dval[2][p] : dval[3][p]));
+          break;
+        }
+        case FD_X_PUSH_FIELD: {
+          FD_X_SPILL()
+          ++sp;
           const T* f = P.field[P.arg[pc]] + idx0;
 #pragma unroll
           for (int p = 0; p < PT; ++p)
             if (active[p]) top[p] = __ldg(f + p * (int)blockDim.x);
-        } else {
-#pragma unroll
-          for (int p = 0; p < PT; ++p) top[p] = P.imm[pc];
+          break;
         }
-      } else if (op >= FD_X_ADD && op <= FD_X_POW) {
-        --sp;                          // b = top (registers), a = the slot below
+        case FD_X_PUSH_IMM: {
+          FD_X_SPILL()
+          ++sp;
 #pragma unroll
-        for (int p = 0; p < PT; ++p) {
-          const T a = stack[sp - 1][p][tid], b = top[p];
-          top[p] = op == FD_X_ADD ? add_rn(a, b)
-                   : op == FD_X_SUB ? sub_rn(a, b)
-                   : op == FD_X_MUL ? mul_rn(a, b)
-                   : op == FD_X_DIV ? div_rn(a, b) : pow_dev<T>(a, b);
+          for (int p = 0; p < PT; ++p) top[p] = imm;
+          break;
         }
-      } else {
-        const T imm = P.imm[pc];
-#pragma unroll
-        for (int p = 0; p < PT; ++p) {
-          const T a = top[p];
-          T r;
-          switch (op) {
-            case FD_X_NEG: r = -a; break;
-            case FD_X_ADD_IMM: r = add_rn(a, imm); break;
-            case FD_X_SUB_IMM: r = sub_rn(a, imm); break;
-            case FD_X_MUL_IMM: r = mul_rn(a, imm); break;
-            case FD_X_DIV_IMM: r = div_rn(a, imm); break;
-            case FD_X_POW_IMM: r = pow_dev<T>(a, imm); break;
-            case FD_X_SQUARE: r = mul_rn(a, a); break;
-            case FD_X_RECIP: r = div_rn((T)1, a); break;
-            default: r = sqrt_dev<T>(a); break;
-          }
-          top[p] = r;
-        }
+        case FD_X_NEG: FD_X_EACH(-a) break;
+        case FD_X_ADD: FD_X_PAIR(add_rn(a, b)) break;
+        case FD_X_SUB: FD_X_PAIR(sub_rn(a, b)) break;
+        case FD_X_MUL: FD_X_PAIR(mul_rn(a, b)) break;
+        case FD_X_DIV: FD_X_PAIR(div_rn(a, b)) break;
+        case FD_X_POW: FD_X_PAIR(pow_dev<T>(a, b)) break;
+        case FD_X_ADD_IMM: FD_X_EACH(add_rn(a, imm)) break;
+        case FD_X_SUB_IMM: FD_X_EACH(sub_rn(a, imm)) break;
+        case FD_X_MUL_IMM: FD_X_EACH(mul_rn(a, imm)) break;
+        case FD_X_DIV_IMM: FD_X_EACH(div_rn(a, imm)) break;
+        case FD_X_POW_IMM: FD_X_EACH(pow_dev<T>(a, imm)) break;
+        case FD_X_SQUARE: FD_X_EACH(mul_rn(a, a)) break;
+        case FD_X_RECIP: FD_X_EACH(div_rn((T)1, a)) break;
+        default: FD_X_EACH(sqrt_dev<T>(a)) break;
       }
     }
+#undef FD_X_EACH
+#undef FD_X_PAIR
 #undef FD_X_SPILL
 #pragma unroll
     for (int p = 0; p < PT; ++p)
