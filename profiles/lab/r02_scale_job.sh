@@ -29,6 +29,8 @@ for N in 1 2 4 8; do
 done
 run 8 n8_k100 --steps 100 --warmup 5 --timeline gpurun_out/r02_timeline_n8_k100.json
 for N in 2 4 8; do
-  run $N strong_n${N}_k100 --steps 100 --warmup 5 --scaling strong --no-workloads
+  run $N strong_n${N}_k100 --steps 100 --warmup 5 --scaling strong --no-workloads --timeline gpurun_out/r02_timeline_strong_n${N}_k100.json
 done
 FD_B200_NO_P2P=1 run 8 n8_k20_nccl --steps 20 --warmup 5 --no-workloads
+FD_B200_NO_SEQ=1 run 8 n8_k20_noseq --steps 20 --warmup 5 --no-workloads
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29514 profiles/pcie_probe.py 2>/dev/null | tee gpurun_out/r02_pcie_probe_n8.txt
