@@ -161,7 +161,7 @@ static int launch_halo_exchange(const fd_halo_link_t* links, int nlinks, void* c
 // boundary planes and their exchange on the communication stream, the events
 // that order them -- one call instead of a dozen calls from Python.
 struct Seq {
-  cudaEvent_t start, rims, halo;
+  cudaEvent_t start, rims, halo, side_start, side_done;
   unsigned* counter;
   bool halo_recorded;
 };
@@ -339,6 +339,8 @@ int fd_seq_create(void** seq_out) {
   cudaError_t e = cudaEventCreateWithFlags(&q->start, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&q->rims, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&q->halo, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&q->side_start, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&q->side_done, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaMalloc((void**)&q->counter, sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMemset(q->counter, 0, sizeof(unsigned));
   if (e != cudaSuccess) {
@@ -357,6 +359,8 @@ int fd_seq_destroy(void* seq) {
   cudaEventDestroy(q->start);
   cudaEventDestroy(q->rims);
   cudaEventDestroy(q->halo);
+  cudaEventDestroy(q->side_start);
+  cudaEventDestroy(q->side_done);
   cudaFree(q->counter);
   delete q;
   return 0;
@@ -370,6 +374,42 @@ int fd_seq_wait_halo(void* seq, void* stream) {
   cudaError_t e = cudaStreamWaitEvent((cudaStream_t)stream, q->halo, 0);
   if (e != cudaSuccess) return fail("fd_seq_wait_halo: %s", cudaGetErrorString(e));
   return 0;
+}
+
+// one statement as several boxes (interior box + rim slabs of a fixed-boundary
+// problem): the first box on `stream`, the others beside it on `side_stream`
+static int step_boxes(bool f64, void* seq, const fd_fused_t* desc, int nboxes, const int32_t* boxes, void* stream, void* side_stream) {
+  using namespace fdb;
+  if (!seq || !desc || !boxes || nboxes < 1) return fail("fd_fused_step_boxes: bad argument");
+  Seq* q = (Seq*)seq;
+  cudaStream_t base = (cudaStream_t)stream, side = (cudaStream_t)side_stream;
+  const bool beside = side_stream != nullptr && nboxes > 1;
+  if (beside) {
+    FD_CUDA(cudaEventRecord(q->side_start, base), "fd_fused_step_boxes");
+    FD_CUDA(cudaStreamWaitEvent(side, q->side_start, 0), "fd_fused_step_boxes");
+  }
+  for (int i = 0; i < nboxes; ++i) {
+    fd_fused_t d = *desc;
+    for (int a = 0; a < 3; ++a) {
+      d.box_lo[a] = boxes[6 * i + 2 * a];
+      d.box_hi[a] = boxes[6 * i + 2 * a + 1];
+    }
+    void* where = (beside && i > 0) ? side_stream : stream;
+    const int rc = f64 ? fd_fused_step_f64(&d, where) : fd_fused_step_f32(&d, where);
+    if (rc) return rc;
+  }
+  if (beside) {
+    FD_CUDA(cudaEventRecord(q->side_done, side), "fd_fused_step_boxes");
+    FD_CUDA(cudaStreamWaitEvent(base, q->side_done, 0), "fd_fused_step_boxes");
+  }
+  return 0;
+}
+
+int fd_fused_step_boxes_f64(void* seq, const fd_fused_t* desc, int nboxes, const int32_t* boxes, void* stream, void* side_stream) {
+  return step_boxes(true, seq, desc, nboxes, boxes, stream, side_stream);
+}
+int fd_fused_step_boxes_f32(void* seq, const fd_fused_t* desc, int nboxes, const int32_t* boxes, void* stream, void* side_stream) {
+  return step_boxes(false, seq, desc, nboxes, boxes, stream, side_stream);
 }
 
 int fd_slab_step_f64(void* seq, const fd_slab_step_t* step) { return fdb::slab_step<double>(seq, step); }

@@ -350,6 +350,15 @@ class Engine:
         self._event_next = (self._event_next + 1) % len(self._events)
         return self._events[self._event_next]
 
+    def _sequencer(self):
+        """The library-side holder of the events (and the ticket word) that native
+        multi-launch calls use; made on first use, None on the CPU stand-in."""
+        if self.seq is None and self.dev.copy_stream is not None:
+            handle = C.c_void_p()
+            nat.check(nat.lib.fd_seq_create(C.byref(handle)))
+            self.seq = handle
+        return self.seq
+
     def _sole_ghost_reader(self, st, t):
         """True when at most one statement of the current step differentiates
         level ``t`` of this field along the decomposed axis."""
@@ -720,6 +729,15 @@ class Engine:
                 # (the expression kernel has a single instantiation: nothing to gain from an interior box)
                 boxes = self._box_cache[bkey] = self._split_boxes(d, piece) if top is None else [piece]
             rim_stream = self.dev.rim_stream if len(boxes) > 1 else None
+            if rim_stream is not None and top is None and self.native_seq and self._sequencer() is not None:
+                # interior box + rim slabs, their two events and two stream waits in one native call
+                packed = self._box_cache.get(("packed",) + bkey)
+                if packed is None:
+                    packed = self._box_cache[("packed",) + bkey] = (C.c_int32 * (6 * len(boxes)))(
+                        *[v for box in boxes for a in range(3) for v in box[a]])
+                nat.check(nat.fn("fd_fused_step_boxes", self.dtype)(self.seq, C.addressof(d), len(boxes), packed, base_ptr,
+                                                                    rim_stream.cuda_stream))
+                return
             if rim_stream is not None:
                 # the rim slabs read the same level and write disjoint points:
                 # they run beside the interior box instead of after it
@@ -782,10 +800,7 @@ class Engine:
         step, states = cached
         if [id(s) for s in states] != [id(s) for s in eager]:
             return False
-        if self.seq is None:
-            handle = C.c_void_p()
-            nat.check(nat.lib.fd_seq_create(C.byref(handle)))
-            self.seq = handle
+        self._sequencer()
         for a in range(3):
             base_desc.box_lo[a], base_desc.box_hi[a] = region[a]
         for j, st in enumerate(eager):

@@ -138,6 +138,8 @@ SIGNATURES = {
     "fd_seq_wait_halo": (C.c_int, [C.c_void_p, C.c_void_p]),
     "fd_slab_step_f64": (C.c_int, [C.c_void_p, C.POINTER(SlabStep)]),
     "fd_slab_step_f32": (C.c_int, [C.c_void_p, C.POINTER(SlabStep)]),
+    "fd_fused_step_boxes_f64": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fd_fused_step_boxes_f32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 SIGNATURES["fd_fused_nested_static_f64"] = (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p])
 FD_STATIC_SCRATCH_BYTES = 16 * 1024 * 1024

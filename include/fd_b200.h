@@ -431,6 +431,14 @@ int fd_seq_wait_halo(void* seq, void* stream);
 int fd_slab_step_f64(void* seq, const fd_slab_step_t* step);
 int fd_slab_step_f32(void* seq, const fd_slab_step_t* step);
 
+/* fd_fused_step for a list of boxes in one call (the interior box and the rim
+ * slabs of a fixed-boundary statement, FD.py:1058-1105 ranges): boxes[i] =
+ * {lo0, hi0, lo1, hi1, lo2, hi2}; box 0 runs on `stream`, the others beside it
+ * on `side_stream` (NULL: all on `stream`), and `stream` has waited for them
+ * when the call returns.  `seq` provides the two events. */
+int fd_fused_step_boxes_f64(void* seq, const fd_fused_t* desc, int nboxes, const int32_t* boxes, void* stream, void* side_stream);
+int fd_fused_step_boxes_f32(void* seq, const fd_fused_t* desc, int nboxes, const int32_t* boxes, void* stream, void* side_stream);
+
 #ifdef __cplusplus
 }
 #endif
