@@ -23,12 +23,15 @@ def fd():
     return fd
 
 
-def _run(fd, workload, shape, steps, ic, dtype=None):
-    """Two steps of the benchmark model; returns (final level, [kernel records])."""
+def _run(fd, workload, shape, steps, ic, dtype=None, native_boxes=True):
+    """Two steps of the benchmark model; returns (final level, [kernel records]).
+    native_boxes=False: the boxes of a statement are launched one by one from
+    Python (so that every launch can be recorded) instead of by one native call."""
     import finite_difference._native as nat
     m, F, step = bench.build_model(fd, workload, steps + 1, ic, history="last", shape=shape, dtype=dtype)
     step()                                   # creates the engine
     eng = m._engine
+    eng.native_seq = native_boxes
     seen = []
     for name in ("fd_fused_step", "fd_fused_pair"):
         inner = eng._fn[name]
@@ -59,10 +62,12 @@ def test_config3_512_cubed_lean_kernel_chunk8(fd):
 def test_config2_8192_squared_interior_box_and_rims(fd):
     shape = (8192, 8192)
     ic = np.random.default_rng(4).random(shape)
-    got, seen, stats = _run(fd, "c2", shape, 2, ic)
     want, _ = O.run_heat(shape, 3, False, bench.K_DIFF, bench.DT, ic, keep_dot=False)
+    got, _, stats = _run(fd, "c2", shape, 2, ic)                       # as the benchmark runs it: one native call per statement
     assert np.array_equal(got, want[2], equal_nan=True)
     assert stats["fused"] == 2 and stats["unfused_statements"] == 0
+    got, seen, stats = _run(fd, "c2", shape, 2, ic, native_boxes=False)   # the same boxes, launch by launch
+    assert np.array_equal(got, want[2], equal_nan=True)
     lean = [s for s in seen if s.startswith("star_lean")]
     rims = [s for s in seen if not s.startswith("star_lean")]
     assert lean and all("axes=4" in s and "chunk=8" in s for s in lean), seen
