@@ -313,7 +313,9 @@ class Engine:
         self._halo_done = None            # comm stream: the exchange issued last has completed
         self.seq = None                   # native sequencer of slab steps (fd_seq_create), made on first use
         self.native_seq = os.environ.get("FD_B200_NO_SEQ", "0") != "1"
-        self._seq_steps = {}              # id(descriptor) -> (fd_slab_step_t, states in link order) or None
+        self._seq_steps = {}              # statement key -> (fd_slab_step_t, states in link order) or None
+        self._slab_fast = {}              # plan key -> (fd_slab_step_t, byref, states, ring slots): the per-step short cut
+        self._slab_step_fn = nat.fn("fd_slab_step", self.dtype) if hasattr(nat.lib, "fd_slab_step_f64") else None
         self._ticket = None               # device word of fd_halo_exchange
         self.closed = False
         self._box_cache = {}
@@ -394,6 +396,7 @@ class Engine:
             nat.lib.fd_seq_destroy(self.seq)
             self.seq = None
         self._seq_steps = {}
+        self._slab_fast = {}
         for st in self.states.values():
             if st.peer:
                 st.peer.retire(self.n_t)
@@ -670,6 +673,7 @@ class Engine:
                 self._plans.clear()
                 self._box_cache.clear()
                 self._seq_steps.clear()
+                self._slab_fast.clear()
             self._plans[key] = plan
         d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux, inner_plans, nested = plan
         for src_state, offset, slab in sources:
@@ -679,6 +683,7 @@ class Engine:
                 del self._plans[key]
                 self._box_cache.clear()
                 self._seq_steps.clear()
+                self._slab_fast.clear()
                 return False
             if slab:
                 src_state.refresh_ghosts(t + offset)
@@ -696,6 +701,24 @@ class Engine:
                 d.nan_count[l] = ls.counts.data_ptr() + 8 * (t + 1)
         for l, dim3, side, ls, dim in dyn_faces:
             d.face[l][dim3][side] = ls.face_ptr(dim, side, t + 1)
+        fast = self._slab_fast.get(key)
+        if fast is not None and not all(self._sole_ghost_reader(st, t) for st in fast[2]):
+            fast = None          # another statement of this step reads the same ghost planes: the general path decides
+        if fast is not None:
+            # a slab statement that went through fd_slab_step before: its step
+            # descriptor is complete, only the level number of the exchange changes
+            step, ref, states, slots = fast
+            for j, st in enumerate(states):
+                step.link[j].value = st.peer.base + t + 2
+            step.compute_stream = self.stream
+            nat.check(self._slab_step_fn(self.seq, ref))
+            for st, k in zip(states, slots):
+                st.halo_ok[k], st.halo_event[k] = True, "seq"
+            n, stats = len(states), self.stats
+            stats["halo_exchanges"] = stats.get("halo_exchanges", 0) + n
+            stats["peer_halo_exchanges"] = stats.get("peer_halo_exchanges", 0) + n
+            stats["native_slab_steps"] = stats.get("native_slab_steps", 0) + 1
+            return True
         region = [[0, dims3[a]] for a in range(3)]
         if self.H:
             # only the owned planes are computed; the domain faces of the slab
@@ -808,6 +831,10 @@ class Engine:
         step.desc = C.addressof(d)
         step.compute_stream, step.comm_stream = self.stream, dev.comm_stream.cuda_stream
         nat.check(nat.fn("fd_slab_step", self.dtype)(self.seq, C.byref(step)))
+        if kind != 1 and top_level_plan_key(cache_key):
+            # (fused / expression statements have a cached plan whose descriptor lives on:
+            # from the next step of this ring parity on _try_fused calls the library directly)
+            self._slab_fast[cache_key] = (step, C.byref(step), list(eager), [st.slot_index(t + 1) for st in eager])
         for st in eager:
             k = st.slot_index(t + 1)
             st.halo_ok[k], st.halo_event[k] = True, "seq"
@@ -1309,6 +1336,7 @@ class Engine:
         self._plans.clear()
         self._box_cache.clear()
         self._seq_steps.clear()
+        self._slab_fast.clear()
         st = self.states.get(id(field))
         if st is not None:
             st.faces = None
@@ -1422,6 +1450,11 @@ def _compile_expr(node):
             or len(code) > nat.FD_EXPR_MAX_CODE or depth[1] > nat.FD_EXPR_MAX_STACK):
         return None
     return ders, leaves, code
+
+
+def top_level_plan_key(key):
+    """Plan keys of fused statements are (id(field), parity, chain ids, statement key)."""
+    return isinstance(key, tuple) and len(key) == 4 and isinstance(key[1], int)
 
 
 def _has_nested_der(node):
