@@ -432,8 +432,9 @@ class Engine:
             if self.H > min(self.slab.counts):
                 raise Exception(f"stencils reach {self.H} planes along {self.slab.axis}, more than the "
                                 f"{min(self.slab.counts)} planes of the smallest slab")
-        for f in self.model.fields:          # initial levels go up before the first launch
-            self.state(f)
+        if len(self.states) < len(self.model.fields):
+            for f in self.model.fields:      # initial levels go up before the first launch
+                self.state(f)
         reads_new = set()
         self._ghost_readers = readers = {}
         keys = [None] * len(stmts)
@@ -474,10 +475,11 @@ class Engine:
             else:
                 self._generic_integrate(field, t)
             self.stats["unfused_statements"] += 1
-        for f in self.model.fields:
-            st = self.state(f)
-            if not st.constant and self.wants_level(t + 1):
-                self.snapshot(st, t + 1)
+        if self.wants_level(t + 1):
+            for f in self.model.fields:
+                st = self.state(f)
+                if not st.constant:
+                    self.snapshot(st, t + 1)
 
     @staticmethod
     def _find_chain(stmts, i, field):
