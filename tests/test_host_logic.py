@@ -325,3 +325,34 @@ def test_der_of_a_computed_expression_is_fused(name, launches):
         stats = made[-1]._engine.stats
         assert stats["unfused_statements"] == 0 and stats["fused_nested"] == 4, stats
         assert lib.launches - 4 * launches in (1, 2), lib.launches   # + NaN count (and device fill) of the initial level
+
+
+def test_model_close_keeps_results_and_refuses_further_steps():
+    """Model.close() (additive): the history is brought up to date first, the
+    device state goes, and a closed model cannot be advanced."""
+    import contextlib
+    import io
+    import numpy as np
+    from oracle import fd_numpy as O
+    shape, n_t = (6, 8), 5
+    ic = np.random.default_rng(9).random(shape)
+    with fake_native.installed():
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model({"t": np.arange(n_t) * 1e-3, "x": np.arange(shape[0]) * 1.0, "y": np.arange(shape[1]) * 1.0}, "t",
+                         periodic=("x", "y"))
+            T = fd.Field(m, "T", n_time_ders=1)
+            d2 = fd.Stencil([-1, 0, 1], 2)
+            T.set_IC_values(ic)
+            for _ in range(3):
+                T.dot.assign_update(0.1 * (d2.der(T.prev, "x") + d2.der(T.prev, "y")))
+                T.time_integrate_update()
+                m.increment_time()
+            m.close()
+            m.close()                                    # idempotent
+            want, _ = O.run_heat(shape, n_t, True, 0.1, 1e-3, ic)
+            assert np.array_equal(T.data[:4], want[:4], equal_nan=True)
+            assert m._engine.states == {}
+            T.dot.assign_update(0.1 * (d2.der(T.prev, "x") + d2.der(T.prev, "y")))
+            T.time_integrate_update()
+            with pytest.raises(Exception, match="closed"):
+                m.increment_time()
