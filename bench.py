@@ -42,6 +42,7 @@ from __future__ import annotations
 
 import argparse
 import contextlib
+import gc
 import io
 import json
 import os
@@ -300,6 +301,16 @@ def timed_steps(torch, dist, m, step, K, world, timeline=False):
     return out
 
 
+def release_garbage(torch):
+    """A closed model is a cycle of Python objects (model <-> fields <-> recorded
+    closures) that still owns device and pinned memory until the cycle collector
+    has run; left lying around it made the next workload's host cost per step 2-3x
+    higher (profiles/lab/diag_c2_host.py: 0.075 ms fresh, 0.22 ms after a closed
+    512^3 model, 0.077 ms after gc.collect())."""
+    gc.collect()
+    torch.cuda.empty_cache()
+
+
 def max_over_ranks(torch, dist, value, world):
     if world == 1:
         return float(value)
@@ -328,7 +339,7 @@ def run_device_resident(torch, dist, fd, workload, ic, K, W, world, scaling="wea
     got["host_enqueue_ms"] = max_over_ranks(torch, dist, got["host_enqueue_ms"], world)
     m.close()
     del m, F, step
-    torch.cuda.empty_cache()
+    release_garbage(torch)
     return got
 
 
@@ -532,6 +543,8 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=_nccl_options())
     import finite_difference as fd
+    gc.collect()
+    gc.freeze()          # what the imports created stays out of later collections
 
     desc, shape, bpp = WORKLOADS[args.workload]
     K, W = args.steps, args.warmup
@@ -611,6 +624,8 @@ def run_b200(args):
         torch.cuda.synchronize()
         secs = time.perf_counter() - t0
         m2.close()
+        del m2, F2, step2
+        release_garbage(torch)
         return secs, out
 
     end_to_end(W)                            # warm-up: allocator pools (device ring, pinned host level)
@@ -645,7 +660,7 @@ def run_b200(args):
                                    "d2h_bytes_per_step": {"last": bytes_level / hk, 8: 2 * 2 * bytes_level / hk,
                                                           "all": 2 * bytes_level}[policy],
                                    "policy": f"Model(history={policy!r}); T and T.dot levels kept"}
-        torch.cuda.empty_cache()
+        release_garbage(torch)
 
     # ---- the other configurations, same process, same timing rules ---------
     others = {}

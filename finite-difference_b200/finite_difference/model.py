@@ -206,6 +206,10 @@ class Model:
             for field in self.fields:
                 self._engine.sync_history(field)
         self._engine.close()
+        # earlier closed models are cycles of Python objects that still own device
+        # and pinned memory until the cycle collector has run
+        import gc
+        gc.collect()
 
 
 def _axis_problem(axis_name, vals):
