@@ -301,14 +301,15 @@ def timed_steps(torch, dist, m, step, K, world, timeline=False):
     return out
 
 
-def release_garbage(torch):
+def release_garbage(torch, empty_cache=True):
     """A closed model is a cycle of Python objects (model <-> fields <-> recorded
     closures) that still owns device and pinned memory until the cycle collector
     has run; left lying around it made the next workload's host cost per step 2-3x
     higher (profiles/lab/diag_c2_host.py: 0.075 ms fresh, 0.22 ms after a closed
     512^3 model, 0.077 ms after gc.collect())."""
     gc.collect()
-    torch.cuda.empty_cache()
+    if empty_cache:
+        torch.cuda.empty_cache()
 
 
 def max_over_ranks(torch, dist, value, world):
@@ -625,7 +626,7 @@ def run_b200(args):
         secs = time.perf_counter() - t0
         m2.close()
         del m2, F2, step2
-        release_garbage(torch)
+        release_garbage(torch, empty_cache=False)     # (the allocator's pools stay warm for the timed run)
         return secs, out
 
     end_to_end(W)                            # warm-up: allocator pools (device ring, pinned host level)
