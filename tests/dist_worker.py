@@ -47,6 +47,14 @@ def peer_halo_case(fd, world):
     want, _ = O.run_acoustic(shape, n_t, 1.0, 0.25, 0.1, ic.astype(np.float32), dtype=np.float32)
     assert np.array_equal(p.data, want.astype(np.float64), equal_nan=True)
     assert (m._engine.stats.get("peer_halo_exchanges", 0) >= n_t - 2) == direct, m._engine.stats
+    # slabs of unequal thickness (one plane more on the first ranks): other ghost offsets in the neighbours' rings
+    shape = (8 * world + world - 1, 24, 64)
+    ic = np.random.default_rng(72).random(shape)
+    for periodic in (True, False):
+        m, T = _heat(fd, shape, n_t, periodic, 0.1, 1e-3, ic)
+        want, _ = O.run_heat(shape, n_t, periodic, 0.1, 1e-3, ic)
+        assert np.array_equal(T.data, want, equal_nan=True)
+        assert (m._engine.stats.get("peer_halo_exchanges", 0) >= n_t - 2) == direct, m._engine.stats
 
 
 def cross_diffusion_case(fd, world):
