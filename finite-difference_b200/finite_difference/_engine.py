@@ -457,7 +457,7 @@ class Engine:
                         readers[(f, t + rel)] = readers.get((f, t + rel), 0) + 1
         memo = {}
         consumed = set()
-        if self.fuse and self.fuse_pairs and self._try_pair(stmts, t, reads_new):
+        if self.fuse and self.fuse_pairs and self._try_pair(stmts, t, reads_new, keys):
             consumed = set(range(len(stmts)))
             self.stats["fused_pairs"] = self.stats.get("fused_pairs", 0) + 1
         for i, (kind, field, node) in enumerate(stmts):
@@ -1024,113 +1024,56 @@ class Engine:
 
 
     # ------------------------------------------------- fused staggered pair
-    def _try_pair(self, stmts, t, reads_new):
+    def _try_pair(self, stmts, t, reads_new, keys=None):
         """The whole step is  v_a += dt*c_a*up.der(p.prev, a)  for some axes a, then
         p += dt*c*(sum_a down.der(v_a.new, a))  (cell/edge leapfrog):
-        one launch of fd_fused_pair instead of len(axes)+1 fused statements."""
+        one launch of fd_fused_pair instead of len(axes)+1 fused statements.
+        The match is made once per form of the step and ring parity; afterwards
+        only the per-step words of the descriptor are patched."""
         n = len(stmts)
         if n < 4 or n % 2 or n > 8:
             return False
-        kinds = [k for k, _, _ in stmts]
-        if kinds != ["assign", "integrate"] * (n // 2):
+        pkey = ("pair", t & 1, tuple(id(f) for _, f, _ in stmts),
+                tuple(keys) if keys is not None else tuple(None if nd is None else nd.key() for _, _, nd in stmts))
+        plan = self._plans.get(pkey, 0)
+        if plan == 0:
+            plan = self._build_pair_plan(stmts, t)
+            if len(self._plans) >= 64:
+                self._plans.clear()
+                self._box_cache.clear()
+                self._seq_steps.clear()
+                self._slab_fast.clear()
+            self._plans[pkey] = plan          # (None: this form of step is not a staggered pair)
+        if plan is None:
             return False
-        for i in range(0, n, 2):                       # assign(F.dot) directly followed by integrate(F)
-            if stmts[i][1]._parent is not stmts[i + 1][1] or stmts[i + 1][1]._parent is not None:
-                return False
-        p_field = stmts[n - 1][1]
-        p_state = self.state(p_field)
-        dims3 = p_state.dims3
-        vn = 16 // self.dtype.itemsize
-        if dims3 is None or dims3[2] % vn or dims3[2] < 3 * vn or len(p_field._slice_shape) > 3:
+        d, p_field, p_state, pd_state, axes, region, pad = plan
+        try:
+            if self.H:
+                p_state.refresh_ghosts(t)
+            d.p_prev = p_state.level(t).data_ptr()
+            wants = self.wants_level(t + 1)
+            outs = []
+            for ax, vfield, vs, vds, along_slab in axes:
+                if along_slab:
+                    vs.refresh_ghosts(t)
+                ax.v_prev = vs.level(t).data_ptr()
+        except RuntimeError:                  # a level is not resident: the general paths report it
+            del self._plans[pkey]
             return False
-        shape = tuple(p_field._slice_shape)
-        pad = 3 - len(shape)
-        down = _match_statement(stmts[n - 2][2])
-        if down is None:
-            return False
-        terms, posts = down
-        if len(terms) != n // 2 - 1 or posts not in ([], [(nat.POST_MUL, posts[0][1] if posts else 0.0, None)]):
-            return False
-        ups = {}
-        for i in range(0, n - 2, 2):                   # the velocity statements
-            m = _match_statement(stmts[i][2])
-            if m is None:
-                return False
-            (uterms, uposts), vfield = m, stmts[i + 1][1]
-            if len(uterms) != 1 or uposts not in ([], [(nat.POST_MUL, uposts[0][1] if uposts else 0.0, None)]):
-                return False
-            der, _, pre, negate = uterms[0]
-            if (negate or (pre is not None and uposts) or der.shifts != (-1, 0) or not isinstance(der.a, Leaf)
-                    or der.a.field is not p_field or der.a.t != t or tuple(vfield._slice_shape) != shape):
-                return False
-            # `c * der` is matched as a pre-scaled term; as a post-multiplication it rounds the same
-            c_up = pre if pre is not None else (uposts[0][1] if uposts else 1.0)
-            ups[id(vfield)] = (vfield, der, c_up)
-        fields = [p_field, p_field.dot] + [f for f, _, _ in ups.values()] + [f.dot for f, _, _ in ups.values()]
-        if any(f._bc_locations for f in fields) or len(ups) != len(terms):
-            return False
-        d = nat.Pair()
-        used = set()
-        for k, (der, subtract, pre, negate) in enumerate(terms):
-            leaf = der.a
-            got = ups.get(id(leaf.field)) if isinstance(leaf, Leaf) else None
-            if (got is None or leaf.t != t + 1 or pre is not None or negate or der.shifts != (0, 1)
-                    or got[1].axis != der.axis or der.axis in used):
-                return False
-            used.add(der.axis)
-            vfield, uder, c_up = got
-            slab_axis = self.H and der.axis == 0
-            # (the ders' own flags are global facts, the same on every rank: a fixed
-            # axis needs the range predicates of the general kernels, also along the slabs)
-            if not der.periodic or not uder.periodic:
-                return False
-            if slab_axis and self.H != 1:
-                return False
-            ax = d.ax[k]
-            ax.axis, ax.periodic, ax.subtract = der.axis + pad, 0 if slab_axis else 1, 1 if subtract else 0
-            ax.c_up = c_up
-            ax.up = nat.make_stencil(uder.shifts, uder.weights, uder.scale, self.exact_div)
-            ax.down = nat.make_stencil(der.shifts, der.weights, der.scale, self.exact_div)
-        # every axis of the grid that is not differentiated must not matter; every
-        # differentiated one is periodic or the slab axis: nothing can be NaN-masked
-        if self.H and 0 not in used:
-            return False
-
-        # ---- all checks passed: claim levels and launch
-        for a in range(3):
-            d.n[a] = dims3[a]
-        d.naxes = len(terms)
-        if self.H:
-            p_state.refresh_ghosts(t)
-        d.p_prev = p_state.level(t).data_ptr()
-        d.c_down = posts[0][1] if posts else 1.0
-        d.dt = float(self.model.dt)
-        outs = []
-        for k, (der, _, _, _) in enumerate(terms):
-            vfield = der.a.field
-            vs, vds = self.state(vfield), self.state(vfield.dot)
-            if self.H and der.axis == 0:
-                vs.refresh_ghosts(t)
-            ax = d.ax[k]
-            ax.v_prev = vs.level(t).data_ptr()
+        for ax, vfield, vs, vds, along_slab in axes:
             ax.v_out = vs.claim(t + 1).data_ptr()
             ax.v_nan_count = vs.counts.data_ptr() + 8 * (t + 1)
-            want = id(vfield.dot) in reads_new or self.wants_level(t + 1)
+            want = wants or id(vfield.dot) in reads_new
             ax.vdot_out = vds.claim(t + 1).data_ptr() if want else 0
             if not want:
                 vds.held[0] = -1
             outs.append(vs)
-        pd_state = self.state(p_field.dot)
         d.p_out = p_state.claim(t + 1).data_ptr()
         d.p_nan_count = p_state.counts.data_ptr() + 8 * (t + 1)
-        want = id(p_field.dot) in reads_new or self.wants_level(t + 1)
+        want = wants or id(p_field.dot) in reads_new
         d.pdot_out = pd_state.claim(t + 1).data_ptr() if want else 0
         if not want:
             pd_state.held[0] = -1
-        d.flags = self.flags.data_ptr()
-        region = [[0, dims3[a]] for a in range(3)]
-        if self.H:
-            region[pad] = [self.H, self.H + p_state.owned0]
         launch = self._fn["fd_fused_pair"]
 
         def run(piece, on=None):
@@ -1142,10 +1085,93 @@ class Engine:
         if eager and self.overlap:
             # (the pair kernel reads the level-t ghosts of p and of the slab-axis velocity,
             # and the statements it replaces are the only ones of the step)
-            self._run_overlapped(run, region, pad, eager, t, {id(st) for st in eager}, seq_desc=(1, d, d, ("pair", t & 1, len(terms))))
+            self._run_overlapped(run, region, pad, eager, t, {id(st) for st in eager},
+                                 seq_desc=(1, d, d, ("pair", t & 1, len(axes))))
         else:
             run(region)
         return True
+
+    def _build_pair_plan(self, stmts, t):
+        """Match the statements of a step against the staggered pair and fill
+        everything of fd_pair_t that does not change from step to step; None if
+        the step has another form."""
+        n = len(stmts)
+        kinds = [k for k, _, _ in stmts]
+        if kinds != ["assign", "integrate"] * (n // 2):
+            return None
+        for i in range(0, n, 2):                       # assign(F.dot) directly followed by integrate(F)
+            if stmts[i][1]._parent is not stmts[i + 1][1] or stmts[i + 1][1]._parent is not None:
+                return None
+        p_field = stmts[n - 1][1]
+        p_state = self.state(p_field)
+        dims3 = p_state.dims3
+        vn = 16 // self.dtype.itemsize
+        if dims3 is None or dims3[2] % vn or dims3[2] < 3 * vn or len(p_field._slice_shape) > 3:
+            return None
+        shape = tuple(p_field._slice_shape)
+        pad = 3 - len(shape)
+        down = _match_statement(stmts[n - 2][2])
+        if down is None:
+            return None
+        terms, posts = down
+        if len(terms) != n // 2 - 1 or posts not in ([], [(nat.POST_MUL, posts[0][1] if posts else 0.0, None)]):
+            return None
+        ups = {}
+        for i in range(0, n - 2, 2):                   # the velocity statements
+            m = _match_statement(stmts[i][2])
+            if m is None:
+                return None
+            (uterms, uposts), vfield = m, stmts[i + 1][1]
+            if len(uterms) != 1 or uposts not in ([], [(nat.POST_MUL, uposts[0][1] if uposts else 0.0, None)]):
+                return None
+            der, _, pre, negate = uterms[0]
+            if (negate or (pre is not None and uposts) or der.shifts != (-1, 0) or not isinstance(der.a, Leaf)
+                    or der.a.field is not p_field or der.a.t != t or tuple(vfield._slice_shape) != shape):
+                return None
+            # `c * der` is matched as a pre-scaled term; as a post-multiplication it rounds the same
+            c_up = pre if pre is not None else (uposts[0][1] if uposts else 1.0)
+            ups[id(vfield)] = (vfield, der, c_up)
+        fields = [p_field, p_field.dot] + [f for f, _, _ in ups.values()] + [f.dot for f, _, _ in ups.values()]
+        if any(f._bc_locations for f in fields) or len(ups) != len(terms):
+            return None
+        d = nat.Pair()
+        used = set()
+        axes = []
+        for k, (der, subtract, pre, negate) in enumerate(terms):
+            leaf = der.a
+            got = ups.get(id(leaf.field)) if isinstance(leaf, Leaf) else None
+            if (got is None or leaf.t != t + 1 or pre is not None or negate or der.shifts != (0, 1)
+                    or got[1].axis != der.axis or der.axis in used):
+                return None
+            used.add(der.axis)
+            vfield, uder, c_up = got
+            slab_axis = bool(self.H) and der.axis == 0
+            # (the ders' own flags are global facts, the same on every rank: a fixed
+            # axis needs the range predicates of the general kernels, also along the slabs)
+            if not der.periodic or not uder.periodic:
+                return None
+            if slab_axis and self.H != 1:
+                return None
+            ax = d.ax[k]
+            ax.axis, ax.periodic, ax.subtract = der.axis + pad, 0 if slab_axis else 1, 1 if subtract else 0
+            ax.c_up = c_up
+            ax.up = nat.make_stencil(uder.shifts, uder.weights, uder.scale, self.exact_div)
+            ax.down = nat.make_stencil(der.shifts, der.weights, der.scale, self.exact_div)
+            axes.append((ax, vfield, self.state(vfield), self.state(vfield.dot), slab_axis))
+        # every axis of the grid that is not differentiated must not matter; every
+        # differentiated one is periodic or the slab axis: nothing can be NaN-masked
+        if self.H and 0 not in used:
+            return None
+        for a in range(3):
+            d.n[a] = dims3[a]
+        d.naxes = len(terms)
+        d.c_down = posts[0][1] if posts else 1.0
+        d.dt = float(self.model.dt)
+        d.flags = self.flags.data_ptr()
+        region = [[0, dims3[a]] for a in range(3)]
+        if self.H:
+            region[pad] = [self.H, self.H + p_state.owned0]
+        return d, p_field, p_state, self.state(p_field.dot), axes, region, pad
 
     # --------------------------------------------------------- unfused path
     def _eval(self, node, memo):
