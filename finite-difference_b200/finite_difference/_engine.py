@@ -241,21 +241,27 @@ class _TempField:
 
 
 class TempState:
-    """Device side of a _TempField: what the plan builder asks of a FieldState."""
+    """Device side of a _TempField: what the plan builder asks of a FieldState.
+    On a slab it has the layout of the fields (ghost planes on either side of the
+    owned planes) so that one descriptor geometry serves both; its ghost planes
+    are never filled -- a der along the decomposed axis of a scratch level is
+    not fused."""
     constant = integrated = wants_ghosts = False
     counts = peer = pooled = None
-    H = 0
 
     def __init__(self, engine, field):
         self.field, self.engine = field, engine
         shape = tuple(field._slice_shape)
-        self.size = self.ext_size = int(np.prod(shape)) if shape else 1
+        self.H = engine.H or 0
+        self.size = int(np.prod(shape)) if shape else 1
         self.owned0 = shape[0] if shape else 1
         self.plane = self.size // self.owned0 if self.owned0 else 0
-        self.ext_shape = shape
-        self.ring = [engine.dev.empty(self.size, engine.dtype)]
+        self.ext_shape = ((self.owned0 + 2 * self.H,) + shape[1:]) if self.H else shape
+        self.ext_size = self.size + 2 * self.H * self.plane
+        self.ring = [engine.dev.empty(self.ext_size, engine.dtype)]
         s = len(shape)
-        self.dims3 = (1,) * (3 - s) + shape if s <= 3 else (int(np.prod(shape[:-2])),) + shape[-2:]
+        ext = self.ext_shape
+        self.dims3 = (1,) * (3 - s) + ext if s <= 3 else ((int(np.prod(ext[:-2])),) + ext[-2:] if not self.H else None)
 
     def slot_index(self, t):
         return 0
@@ -504,9 +510,11 @@ class Engine:
         # its own (one plain-assignment launch), the statement then reads that level
         inner_plans = []
         if _has_nested_der(node):
-            if self.H or not self.fuse_nested:
+            if not self.fuse_nested:
                 return None
-            node, lifted = _lift_nested_ders(node, self.model, t)
+            node, lifted, rewritten = _lift_nested_ders(node, self.model, t)
+            if any(der.slab for der in rewritten):
+                return None      # the scratch level has no ghost planes: unfused path (which says so)
             for leaf, inner in lifted:
                 leaf.field._temp_state = TempState(self, leaf.field)
                 plan = self._build_fused_plan(leaf.field, inner, [], t)
@@ -636,6 +644,10 @@ class Engine:
             scratch = ip[1].ring[0]
             inner_d = ip[0]
             inner_d.out[0] = 0
+            for a in range(3):
+                inner_d.box_lo[a], inner_d.box_hi[a] = 0, ip[6][a]
+            if self.H:
+                inner_d.box_lo[ip[5]], inner_d.box_hi[ip[5]] = self.H, self.H + ip[1].owned0
             hits = 0
             for k in range(d.nterms):
                 if d.term[k].src == scratch.data_ptr():
@@ -652,11 +664,13 @@ class Engine:
 
     def _launch_inner(self, plan):
         """The scratch level of an inner expression (plain assignment, whole level)."""
-        d, _, _, _, _, _, dims3, top, _, inners, _ = plan
+        d, dot_state, _, _, _, pad, dims3, top, _, inners, _ = plan
         for ip in inners:
             self._launch_inner(ip)
         for a in range(3):
             d.box_lo[a], d.box_hi[a] = 0, dims3[a]
+        if self.H:
+            d.box_lo[pad], d.box_hi[pad] = self.H, self.H + dot_state.owned0
         if top is None:
             nat.check(self._fn["fd_fused_step"](C.byref(d), self.stream))
         else:
@@ -1497,10 +1511,11 @@ def _has_nested_der(node):
 
 def _lift_nested_ders(node, model, t):
     """Replace the argument of every der that is not a stored level by a scratch
-    leaf.  Returns (rewritten tree, [(scratch leaf, inner expression)]); equal
+    leaf.  Returns (rewritten tree, [(scratch leaf, inner expression)], [the ders
+    that now read a scratch leaf]); equal
     inner expressions share one scratch level.  (Ders nested deeper stay inside
     the inner expressions: they are lifted when those get their own plans.)"""
-    lifted, by_key = [], {}
+    lifted, by_key, rewritten = [], {}, []
 
     def walk(n):
         if isinstance(n, Der):
@@ -1514,6 +1529,7 @@ def _lift_nested_ders(node, model, t):
             new = Der(leaf, n.shape, n.axis, n.shifts, n.weights, n.scale, n.periodic, n.lo, n.hi, n.n_src, n.n_dst,
                       n.stencil)
             new.slab = n.slab
+            rewritten.append(new)
             return new
         if isinstance(n, Unary):
             a = walk(n.a)
@@ -1524,7 +1540,7 @@ def _lift_nested_ders(node, model, t):
             return n if (a is n.a and b is n.b) else Binary(n.op, a, b)
         return n
 
-    return walk(node), lifted
+    return walk(node), lifted, rewritten
 
 
 def _slab_reach(stmts):

@@ -470,6 +470,32 @@ def nested_staggered_flux(fd, n_t=5):
     return {"T": T.data, "Tdot": T.dot.data}
 
 
+def nested_cross_axis(fd, n_t=5):
+    """Ders of computed expressions that stay clear of the first axis on the
+    outside (so that they can also be fused on slabs, where the first axis is
+    the decomposed one): div_y(kappa grad_y T) + a plain x term, and a mixed
+    second derivative d/dy(0.5 dc/dx) whose INNER der runs along x."""
+    m = fd.Model({"t": np.arange(n_t) * 1e-2, "x": np.arange(12) * 1.0, "y": np.arange(16) * 0.5}, "t",
+                 periodic=("x", "y"))
+    T = fd.Field(m, "T", n_time_ders=1)
+    c = fd.Field(m, "c", n_time_ders=1)
+    kappa = fd.ConstantField(m, "kappa")
+    kappa.set("1+x*y/50")
+    d1 = fd.Stencil([-1, 0, 1], 1)
+    d2 = fd.Stencil([-1, 0, 1], 2)
+    T.set_IC("x*x+y")
+    c.set_IC("x*y+y*y")
+
+    def body():
+        T.dot.assign_update(d1.der(kappa.always * d1.der(T.prev, "y"), "y") + 0.1 * d2.der(T.prev, "x"))
+        c.dot.assign_update(d1.der(0.5 * d1.der(c.prev, "x"), "y"))
+        T.time_integrate_update()
+        c.time_integrate_update()
+
+    _loop(m, body)
+    return {"T": T.data, "c": c.data, "cdot": c.dot.data}
+
+
 def bc_conflict_prints(fd):
     """set_BC on top of set_IC prints the conflict note (FD.py:569-570)."""
     m = fd.Model({"t": range(0, 4), "x": range(0, 6)}, "t")
@@ -513,4 +539,5 @@ ALL = {
     "nested_divgrad": nested_divgrad,
     "nested_burgers": nested_burgers,
     "nested_staggered_flux": nested_staggered_flux,
+    "nested_cross_axis": nested_cross_axis,
 }

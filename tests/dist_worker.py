@@ -81,6 +81,27 @@ def cross_diffusion_case(fd, world):
     assert eng.stats["unfused_statements"] == 0, eng.stats
 
 
+def nested_on_slabs_case(fd):
+    """oracle/scenarios.py:nested_cross_axis on slabs: ders of computed expressions
+    whose outer der stays clear of the decomposed axis are fused there too (scratch
+    level with the fields' ghost layout), one of them with an inner der ALONG the
+    decomposed axis; the golden bits."""
+    from tests.scenario_check import run_and_compare
+    made = []
+    real_model = fd.Model
+
+    def spy(*a, **k):
+        made.append(real_model(*a, **k))
+        return made[-1]
+    fd.Model = spy
+    try:
+        run_and_compare("nested_cross_axis", fd, check_prints=False)
+    finally:
+        fd.Model = real_model
+    stats = made[-1]._engine.stats
+    assert stats["unfused_statements"] == 0 and stats.get("fused_nested") == 8, stats
+
+
 def main():
     backend, names = sys.argv[1], sys.argv[2:]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -103,6 +124,9 @@ def main():
                 continue
             if name == "__cross_diffusion__":
                 cross_diffusion_case(fd, world)
+                continue
+            if name == "__nested_on_slabs__":
+                nested_on_slabs_case(fd)
                 continue
             results = run_and_compare(name, fd, check_prints=False)
             assert results

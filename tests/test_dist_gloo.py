@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SCENARIOS = ["heat3d_periodic", "heat3d_fixed", "heat2d_fixed", "heat2d_time_middle", "wave2d", "wave2d_5pt",
              "wave2d_fixed_nan_spread", "acoustic3d", "acoustic3d_fixed", "flux_1d", "variable_coefficient",
              "burgers_1d", "readme_1d", "acoustic3d_wide", "acoustic2d", "heat4d_periodic", "heat1d_odd_dx",
-             "cross_diffusion"]
+             "cross_diffusion", "nested_cross_axis"]
 
 
 def _free_port():
@@ -65,6 +65,11 @@ def _launch_once(world, backend, names, extra_env, timeout):
 def test_slab_decomposition_gloo(world):
     names = [n for n in SCENARIOS if not (world == 3 and n in ("acoustic3d_fixed", "heat4d_periodic"))]
     launch(world, "gloo", names)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_nested_ders_are_fused_on_slabs(world):
+    launch(world, "gloo", ["__nested_on_slabs__"])
 
 
 def test_slab_decomposition_gloo_unfused():

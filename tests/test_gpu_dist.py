@@ -30,6 +30,12 @@ def test_slab_decomposition_nccl_unfused():
            {"FD_B200_NO_FUSE": "1"})
 
 
+def test_nested_ders_are_fused_on_slabs_nccl():
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    launch(2, "nccl", ["__nested_on_slabs__"])
+
+
 @pytest.mark.parametrize("world", [2, 4])
 def test_two_statements_read_the_same_ghost_planes(world):
     """`u`'s current level is differentiated along the slab axis by its own
