@@ -429,7 +429,8 @@ class Engine:
         return t % h == 0
 
     # --------------------------------------------------------------- execute
-    def execute(self, stmts):
+    def execute(self, stmts, keys=None):
+        """``keys``: the statements' keys when the caller already has them (replay)."""
         if self.closed:
             raise Exception("the model was closed (Model.close): it cannot be advanced any further")
         t = self.model.time_step
@@ -443,12 +444,13 @@ class Engine:
                 self.state(f)
         reads_new = set()
         self._ghost_readers = readers = {}
+        given = keys
         keys = [None] * len(stmts)
         for i, (_, _, node) in enumerate(stmts):
             if node is not None:
                 # what the statement reads depends on its form alone (levels relative to
                 # the time cursor): worked out once per form, looked up by its key
-                keys[i] = key = node.key()
+                keys[i] = key = given[i] if given is not None else node.key()
                 info = self._stmt_info.get(key)
                 if info is None:
                     new_reads, ghosts = set(), set()
@@ -461,6 +463,7 @@ class Engine:
                 if self.H:
                     for f, rel in info[1]:
                         readers[(f, t + rel)] = readers.get((f, t + rel), 0) + 1
+        self.last_keys = keys
         memo = {}
         consumed = set()
         if self.fuse and self.fuse_pairs and self._try_pair(stmts, t, reads_new, keys):

@@ -99,6 +99,33 @@ class Der(Node):
         return n
 
 
+def stored_level_leaves(stmts):
+    """The distinct leaves (stored time levels of fields that change in time) that
+    the recorded statements read: Model.run replays a step's statements with these
+    moved on in time instead of recording the statements anew."""
+    seen, leaves = set(), []
+
+    def walk(n):
+        if id(n) in seen:
+            return
+        seen.add(id(n))
+        if isinstance(n, Leaf):
+            if not n.field._is_constant:
+                leaves.append(n)
+        elif isinstance(n, (Unary, Der)):
+            walk(n.a)
+        elif isinstance(n, Binary):
+            if isinstance(n.a, Node):
+                walk(n.a)
+            if isinstance(n.b, Node):
+                walk(n.b)
+
+    for _, _, node in stmts:
+        if node is not None:
+            walk(node)
+    return leaves
+
+
 class FieldInstant:
     """Field at one instant of time (FD.py:774-788).  Same attributes as the
     reference -- ``model``, ``edge_axes``, ``name``, ``data`` -- but ``data``

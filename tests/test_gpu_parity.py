@@ -516,3 +516,31 @@ def test_general_power_is_within_the_stated_bound():
     for op, ref in ((nat.OP_SQUARE, a * a), (nat.OP_SQRT, np.sqrt(a)), (nat.OP_RECIP, 1.0 / a), (nat.OP_COPY, a)):
         nat.check(nat.lib.fd_ewise_f64(op, out.data_ptr(), da.data_ptr(), 0, 0.0, n, 0))
         assert np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_model_run_replay_on_the_device(fd):
+    """Model.run(body): the first two steps are recorded, the rest replayed; the
+    oracle's bits after 40 steps (lean kernel) and for the staggered pair."""
+    shape, n_t = (40, 48, 64), 41
+    names = ["x", "y", "z"]
+    ic = np.random.default_rng(51).random(shape)
+    axes = {"t": np.arange(n_t) * 1e-3}
+    for n, a in zip(shape, names):
+        axes[a] = np.arange(n) * 1.0
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = fd.Model(axes, "t", periodic=tuple(names), history=20)
+        T = fd.Field(m, "T", n_time_ders=1)
+        d2 = fd.Stencil([-1, 0, 1], 2)
+        T.set_IC_values(ic)
+    calls = []
+
+    def body():
+        calls.append(1)
+        T.dot.assign_update(0.1 * (d2.der(T.prev, "x") + d2.der(T.prev, "y") + d2.der(T.prev, "z")))
+        T.time_integrate_update()
+    m.run(body)
+    want, _ = O.run_heat(shape, n_t, True, 0.1, 1e-3, ic, keep_dot=False)
+    assert len(calls) == 2 and m.finished
+    for t in (20, 40):
+        assert np.array_equal(T.data_level(t), want[t])
+    assert m._engine.stats["fused"] == 40 and m._engine.stats["unfused_statements"] == 0

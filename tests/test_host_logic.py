@@ -356,3 +356,111 @@ def test_model_close_keeps_results_and_refuses_further_steps():
             T.time_integrate_update()
             with pytest.raises(Exception, match="closed"):
                 m.increment_time()
+
+
+def _models_for_run():
+    """(name, builder) pairs: builder() -> (model, body, fields to compare)."""
+    import contextlib
+    import io
+    import numpy as np
+
+    def heat_fixed_time_bc():
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model({"t": np.arange(9) * 1e-2, "x": np.arange(14) * 1.0, "y": np.arange(16) * 1.0}, "t")
+            T = fd.Field(m, "T", n_time_ders=1)
+            d2 = fd.Stencil([-1, 0, 1], 2)
+            T.set_IC("x+y")
+            T.set_BC("0", "x", "start")
+            T.set_BC("t*y", "x", "end")          # boundary values that change with time
+            T.set_BC("1", "y", "start")
+            T.set_BC("2", "y", "end")
+
+        def body():
+            T.dot.assign_update(0.1 * (d2.der(T.prev, "x") + d2.der(T.prev, "y")))
+            T.time_integrate_update()
+        return m, body, [T, T.dot]
+
+    def wave():
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model({"t": np.arange(9) * 1e-2, "x": np.arange(16) * 1.0, "y": np.arange(16) * 1.0}, "t",
+                         periodic=("x", "y"))
+            u = fd.Field(m, "u", n_time_ders=2)
+            st = fd.Stencil(list(range(-2, 3)), 2)
+            u.set_IC("x*y")
+            u.dot.set_IC("0")
+
+        def body():
+            u.dot.dot.assign_update(0.01 * (st.der(u.prev, "x") + st.der(u.prev, "y")))
+            u.dot.time_integrate_update()
+            u.time_integrate_update()
+        return m, body, [u, u.dot]
+
+    def acoustic():
+        with contextlib.redirect_stdout(io.StringIO()):
+            names = ("x", "y", "z")
+            m = fd.Model({"t": np.arange(9) * 0.1, "x": np.arange(6) * 1.0, "y": np.arange(6) * 1.0, "z": np.arange(8) * 1.0},
+                         "t", periodic=names)
+            p = fd.Field(m, "p", n_time_ders=1)
+            v = {a: fd.Field(m, "v" + a, edge_axes=(a,), n_time_ders=1) for a in names}
+            ce, ec = fd.Stencil([-.5, .5], 1, "cell", "edge"), fd.Stencil([-.5, .5], 1, "edge", "cell")
+            p.set_IC("x*y+z")
+            for a in names:
+                v[a].set_IC("0")
+
+        def body():
+            for a in names:
+                v[a].dot.assign_update(-1.0 * ce.der(p.prev, a))
+                v[a].time_integrate_update()
+            p.dot.assign_update(-0.25 * (ec.der(v["x"].new, "x") + ec.der(v["y"].new, "y") + ec.der(v["z"].new, "z")))
+            p.time_integrate_update()
+        return m, body, [p, v["x"], v["z"]]
+
+    def nested():
+        with contextlib.redirect_stdout(io.StringIO()):
+            m = fd.Model({"t": np.arange(9) * 1e-2, "x": np.arange(40) * 0.5}, "t")
+            u = fd.Field(m, "u", n_time_ders=1)
+            d1, d2 = fd.Stencil([-1, 0, 1], 1), fd.Stencil([-1, 0, 1], 2)
+            u.set_IC("1+x/40")
+            u.set_BC("1", "x", "start")
+            u.set_BC("1.5", "x", "end")
+
+        def body():
+            u.dot.assign_update(-0.5 * d1.der(u.prev * u.prev, "x") + 0.05 * d2.der(u.prev, "x"))
+            u.time_integrate_update()
+        return m, body, [u, u.dot]
+
+    return [("heat_fixed_time_bc", heat_fixed_time_bc), ("wave", wave), ("acoustic", acoustic), ("nested", nested)]
+
+
+@pytest.mark.parametrize("unfused", [False, True])
+def test_model_run_replays_the_recorded_step(unfused, monkeypatch):
+    """Model.run(body) (additive): body is called for the first two steps only,
+    afterwards the recorded statements are replayed with their time levels moved
+    on -- same arrays as the written-out loop, with the history policy, boundary
+    values that depend on time, the staggered pair, a nested der, and the unfused
+    operators; also run(body, k) in pieces mixed with the written-out loop."""
+    import numpy as np
+    if unfused:
+        monkeypatch.setenv("FD_B200_NO_FUSE", "1")
+    with fake_native.installed():
+        for name, build in _models_for_run():
+            m, body, fields = build()
+            while not m.finished:
+                body()
+                m.increment_time()
+            want = [np.array(f.data) for f in fields]
+            m, body, fields = build()
+            calls = []
+            m.run(lambda: (calls.append(1), body()))
+            assert m.finished and len(calls) == 2, (name, len(calls))
+            for f, w in zip(fields, want):
+                assert np.array_equal(f.data, w, equal_nan=True), (name, f.name)
+            m, body, fields = build()
+            m.run(body, 3)
+            body()
+            m.increment_time()
+            m.run(body, 2)
+            m.run(body)
+            assert m.finished
+            for f, w in zip(fields, want):
+                assert np.array_equal(f.data, w, equal_nan=True), (name, f.name, "pieces")
