@@ -313,7 +313,7 @@ class Engine:
         self.poll_every = int(os.environ.get("FD_B200_POLL_EVERY", default_poll))
         self.last_poll = model.time_step
         self.pending_copies = []          # [(state, slot, t, host tensor, event)]
-        self._ghost_readers = {}          # id(field) -> statements of the current step that read its ghost planes
+        self._ghost_readers = {}          # (id(field), level) -> statements of the current step that read its ghost planes
         self._stmt_info = {}              # statement key -> (fields read at the new level, ghost reads relative to t)
         self._events, self._event_next = [], 0     # transient events (recorded and waited for within one call)
         self._halo_done = None            # comm stream: the exchange issued last has completed

@@ -161,6 +161,12 @@ Dimension lengths: {dict(zip(self.model.axes_names,self.model.axes_lengths))}"
     # ---- arithmetic (FD.py:794-869) --------------------------------------
     @staticmethod
     def _operand(operand, models):
+        cls = type(operand)
+        if cls is FieldInstant:                 # the two everyday cases first
+            models.append(operand.model)
+            return operand._node
+        if cls is float or cls is int:
+            return float(operand)
         if isinstance(operand, Field):
             raise TypeError(
                 "Cannot perform arithmetic between a field and a field at a given moment -- use the new or prev properties for both fields")
