@@ -71,12 +71,11 @@ class FieldState:
         s = len(field._slice_shape)
         if s <= 3:
             self.dims3 = (1,) * (3 - s) + tuple(self.ext_shape)
-        elif not self.H:
-            # more than three spatial axes: the leading ones merge into dimension 0
-            # of the kernels' view (fd_term_t.fold_div / fold_mod)
-            self.dims3 = (int(np.prod(self.ext_shape[:-2])),) + tuple(self.ext_shape[-2:])
         else:
-            self.dims3 = None
+            # more than three spatial axes: the leading ones merge into dimension 0
+            # of the kernels' view (fd_term_t.fold_div / fold_mod); on a slab the
+            # outermost of them carries the ghost planes
+            self.dims3 = (int(np.prod(self.ext_shape[:-2])),) + tuple(self.ext_shape[-2:])
         if not self.constant:
             self._discover_array_faces()
         if self.constant:
@@ -549,6 +548,7 @@ class Engine:
             return None
         nd = len(dot_field._slice_shape)
         pad = 3 - nd
+        sdim = max(pad, 0)              # dimension of the kernels' view that holds the decomposed axis
         shape_nd = tuple(dot_field._slice_shape)
 
         top = nat.Expr() if program is not None else None
@@ -587,9 +587,11 @@ class Engine:
             tm.fold_div = tm.fold_mod = 0
             if nd > 3 and der.axis < nd - 2:
                 # one of the merged leading axes (kept extents only: no staggered fixed axis)
-                if der.n_src != shape_nd[der.axis] or tuple(leaf.shape) != shape_nd:
+                if tuple(leaf.shape) != shape_nd or (not der.slab and der.n_src != shape_nd[der.axis]):
                     return None
-                tm.fold_mod = shape_nd[der.axis]
+                if der.slab and der.n_dst != der.n_src:
+                    return None
+                tm.fold_mod = src_state.ext_shape[0] if der.slab else shape_nd[der.axis]
                 tm.fold_div = int(np.prod(shape_nd[der.axis + 1:nd - 2]))
             if der.slab:
                 # the slab is a non-periodic window of the global axis; ghosts hold the neighbours' planes
@@ -635,7 +637,8 @@ class Engine:
         for a in range(3):
             d.rim_lo[a], d.rim_hi[a] = 0, max(dims3[a] - 1, 0)
         if self.H:
-            d.rim_lo[pad], d.rim_hi[pad] = self.H, self.H + dot_state.owned0 - 1
+            unit = dims3[sdim] // dot_state.ext_shape[0]      # merged rows per plane of the decomposed axis (1 up to 3-D)
+            d.rim_lo[sdim], d.rim_hi[sdim] = self.H * unit, (self.H + dot_state.owned0) * unit - 1
         for ip in inner_plans:
             sources += ip[3]
         nested = None
@@ -650,7 +653,8 @@ class Engine:
             for a in range(3):
                 inner_d.box_lo[a], inner_d.box_hi[a] = 0, ip[6][a]
             if self.H:
-                inner_d.box_lo[ip[5]], inner_d.box_hi[ip[5]] = self.H, self.H + ip[1].owned0
+                iu = ip[6][ip[5]] // ip[1].ext_shape[0]
+                inner_d.box_lo[ip[5]], inner_d.box_hi[ip[5]] = self.H * iu, (self.H + ip[1].owned0) * iu
             hits = 0
             for k in range(d.nterms):
                 if d.term[k].src == scratch.data_ptr():
@@ -663,7 +667,7 @@ class Engine:
                         hits += 1
             if hits:
                 nested = (1 if ip[7] is not None else 0, ip[7] if ip[7] is not None else inner_d, scratch)
-        return d, dot_state, levels, sources, dyn_faces, pad, dims3, top, aux, inner_plans, nested
+        return d, dot_state, levels, sources, dyn_faces, sdim, dims3, top, aux, inner_plans, nested
 
     def _launch_inner(self, plan):
         """The scratch level of an inner expression (plain assignment, whole level)."""
@@ -673,7 +677,8 @@ class Engine:
         for a in range(3):
             d.box_lo[a], d.box_hi[a] = 0, dims3[a]
         if self.H:
-            d.box_lo[pad], d.box_hi[pad] = self.H, self.H + dot_state.owned0
+            unit = dims3[pad] // dot_state.ext_shape[0]
+            d.box_lo[pad], d.box_hi[pad] = self.H * unit, (self.H + dot_state.owned0) * unit
         if top is None:
             nat.check(self._fn["fd_fused_step"](C.byref(d), self.stream))
         else:
@@ -739,10 +744,12 @@ class Engine:
             stats["native_slab_steps"] = stats.get("native_slab_steps", 0) + 1
             return True
         region = [[0, dims3[a]] for a in range(3)]
+        unit = 1
         if self.H:
             # only the owned planes are computed; the domain faces of the slab
             # axis sit on the first / last owned plane of the end ranks
-            region[pad] = [self.H, self.H + dot_state.owned0]
+            unit = dims3[pad] // dot_state.ext_shape[0]
+            region[pad] = [self.H * unit, (self.H + dot_state.owned0) * unit]
         launch = self._fn["fd_fused_step" if top is None else "fd_fused_expr"]
         ref = C.byref(d if top is None else top)
         if top is not None:
@@ -804,12 +811,12 @@ class Engine:
             own = {id(st) for st, offset, slab in sources if slab and offset == 0}
             self._run_overlapped(run, region, pad, eager, t,
                                  {id(ls) for ls in eager if id(ls) in own and not aux and self._sole_ghost_reader(ls, t)},
-                                 seq_desc=(0, d, d, key) if top is None else (2, top, d, key))
+                                 seq_desc=(0, d, d, key) if top is None else (2, top, d, key), depth=self.H * unit)
         else:
             run(region)
         return True
 
-    def _native_slab_step(self, seq_desc, region, pad, eager, t, direct_ok):
+    def _native_slab_step(self, seq_desc, region, pad, eager, t, direct_ok, depth):
         """The whole of _run_overlapped in one native call (fd_slab_step) when every
         exchanged field travels through peer memory and no piece needs an
         interior/rim split; False if the statement has to take the Python path."""
@@ -826,12 +833,12 @@ class Engine:
         if cached == 0:
             cached = None
             lo, hi = region[pad]
-            pieces = [[lo, lo + self.H], [hi - self.H, hi], [lo + self.H, hi - self.H]]
+            pieces = [[lo, lo + depth], [hi - depth, hi], [lo + depth, hi - depth]]
             whole = lambda cut: [list(r) if a != pad else cut for a, r in enumerate(region)]
             single = kind != 0 or all(len(self._split_boxes(base_desc, whole(c))) == 1 for c in pieces)
             if single:
                 step = nat.SlabStep()
-                step.kind, step.dim, step.lo, step.hi, step.depth = kind, pad, lo, hi, self.H
+                step.kind, step.dim, step.lo, step.hi, step.depth = kind, pad, lo, hi, depth
                 step.nlinks = len(eager)
                 step.timeout_ns = 20_000_000_000
                 step.flags = self.flags.data_ptr()
@@ -862,17 +869,18 @@ class Engine:
         self.stats["native_slab_steps"] = self.stats.get("native_slab_steps", 0) + 1
         return True
 
-    def _run_overlapped(self, run, region, pad, eager, t, direct_ok=(), seq_desc=None):
+    def _run_overlapped(self, run, region, pad, eager, t, direct_ok=(), seq_desc=None, depth=None):
         """One statement (group) of a slab: the boundary planes and their exchange
         on the high-priority comm stream, the interior beside them on the compute
         stream, so that neither the thin boundary launches nor the trip over
         NVLink add to the step."""
         lo, hi = region[pad]
+        depth = depth or self.H              # ghost depth in rows of the kernels' view (planes up to 3-D)
         piece = lambda cut: [list(r) if a != pad else cut for a, r in enumerate(region)]
-        cuts = ([lo, lo + self.H], [hi - self.H, hi])
-        inner = [lo + self.H, hi - self.H]
+        cuts = ([lo, lo + depth], [hi - depth, hi])
+        inner = [lo + depth, hi - depth]
         dev = self.dev
-        if seq_desc is not None and self._native_slab_step(seq_desc, region, pad, eager, t, direct_ok):
+        if seq_desc is not None and self._native_slab_step(seq_desc, region, pad, eager, t, direct_ok, depth):
             return
         if dev.comm_stream is None or not self.rims_beside:
             # (CPU stand-in, or FD_B200_NO_SIDE_RIMS=1) boundary planes first, their

@@ -102,6 +102,19 @@ def nested_on_slabs_case(fd):
     assert stats["unfused_statements"] == 0 and stats.get("fused_nested") == 8, stats
 
 
+def folded_axes_on_slabs_case(fd, world):
+    """A 4-D heat model cut into slabs: the leading axes merge into dimension 0 of
+    the kernels' view, the decomposed one (with its ghost planes) outermost; one
+    fused launch per statement (three with the boundary planes split off for the
+    overlapped exchange), the oracle's bits."""
+    from tests.nd_cases import run_case
+    for shape, periodic in (((4 * world, 3, 4, 8), True), ((4 * world + 1, 2, 6, 4), True)):
+        got, want, stats = run_case(fd, shape, periodic, 4, n_t=6)
+        assert np.array_equal(got, want, equal_nan=True), shape
+        assert stats["fused"] == 5 and stats["unfused_statements"] == 0, stats
+        assert stats.get("halo_exchanges", 0) >= 5, stats
+
+
 def main():
     backend, names = sys.argv[1], sys.argv[2:]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -127,6 +140,9 @@ def main():
                 continue
             if name == "__nested_on_slabs__":
                 nested_on_slabs_case(fd)
+                continue
+            if name == "__folded_on_slabs__":
+                folded_axes_on_slabs_case(fd, world)
                 continue
             results = run_and_compare(name, fd, check_prints=False)
             assert results

@@ -72,6 +72,11 @@ def test_nested_ders_are_fused_on_slabs(world):
     launch(world, "gloo", ["__nested_on_slabs__"])
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_more_than_three_axes_are_fused_on_slabs(world):
+    launch(world, "gloo", ["__folded_on_slabs__"])
+
+
 def test_slab_decomposition_gloo_unfused():
     launch(2, "gloo", ["heat3d_fixed", "wave2d", "acoustic3d_fixed", "flux_1d", "cross_diffusion"],
            {"FD_B200_NO_FUSE": "1"})

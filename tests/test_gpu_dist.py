@@ -30,6 +30,12 @@ def test_slab_decomposition_nccl_unfused():
            {"FD_B200_NO_FUSE": "1"})
 
 
+def test_more_than_three_axes_are_fused_on_slabs_nccl():
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    launch(2, "nccl", ["__folded_on_slabs__"])
+
+
 def test_nested_ders_are_fused_on_slabs_nccl():
     if _gpus() < 2:
         pytest.skip("needs 2 GPUs")
